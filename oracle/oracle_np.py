@@ -1,0 +1,328 @@
+"""CPU restatement (NumPy, float32) of EvoX's multi-objective environmental-selection path.
+
+TEST INFRASTRUCTURE, NOT PRODUCT.  Only tests/, __graft_entry__.smoke() and
+bench.py's cpu_baseline / --impl reference legs may import this package; the
+product path (evox_b200/) never does and fails loudly without its CUDA library.
+
+Every function cites the reference lines it follows (paths relative to
+/root/reference/).  The reference executes these through jaxlib/XLA, a third-party
+dependency that is absent here and unpinned (pyproject.toml:33-34, `jax>=0.4.16`,
+dev shell ~0.4.20), so this is a restatement of the reference's *source text*.
+
+Pinning (tests/test_oracle_*.py):
+  * every explicit-input known-answer test of the reference for this path
+    (tests/test_non_dominated_sort.py:8-28, tests/test_crowding_distance.py:7-21 and
+    :127-146, tests/test_monitors.py:30-48, tests/test_classic_problems.py:46-54);
+  * the JAX-PRNG-input goldens (tests/test_crowding_distance.py:24-124,
+    tests/test_lsmop.py:19-124, tests/test_maf.py:49-57) with the inputs regenerated
+    by oracle/jax_prng.py;
+  * fixtures under tests/golden/ produced by executing the reference's own .py
+    files on a NumPy-backed jax shim (tests/golden/make_golden.py).
+"""
+from itertools import cycle
+
+import numpy as np
+
+F32 = np.float32
+
+
+# --------------------------------------------------------------------------- #
+# dominance                                                 utils/common.py:88-97
+# --------------------------------------------------------------------------- #
+def dominate_relation(x, y):
+    """A[i, j] = all_k(x[i,k] <= y[j,k]) and any_k(x[i,k] < y[j,k]).
+
+    src/evox/utils/common.py:88-91 (`_dominate`), :94-97 (nested vmap).  IEEE
+    compares: a NaN anywhere in a row makes it neither dominate nor be dominated.
+    """
+    x = np.asarray(x)
+    y = np.asarray(y)
+    nx, ny = x.shape[0], y.shape[0]
+    m = x.shape[1] if x.ndim == 2 else 0
+    out = np.empty((nx, ny), dtype=bool)
+    step = max(1, (1 << 22) // max(1, ny * max(1, m)))
+    with np.errstate(invalid="ignore"):
+        for s in range(0, nx, step):
+            xs = x[s:s + step, None, :]
+            out[s:s + step] = (xs <= y[None, :, :]).all(-1) & (xs < y[None, :, :]).any(-1)
+    return out
+
+
+def rank_from_domination_matrix(dom, count):
+    """Front peeling on a dense matrix.
+
+    src/evox/operators/selection/non_dominate.py:13-29 (the reference's NumPy
+    `host` variant); the jitted variants :74-113 compute the same thing: a row
+    enters front k when its dominator count reaches zero, then every row it
+    dominates loses one, and the row itself is pushed to -1 so it never returns.
+    """
+    count = np.array(count, dtype=np.int64, copy=True)
+    n = dom.shape[0]
+    rank = np.zeros(n, dtype=np.int32)          # jitted variants start from zeros (:74)
+    k = 0
+    front = count == 0
+    while front.any():
+        rank[front] = k
+        count -= dom[front, :].sum(axis=0)
+        count -= front
+        k += 1
+        front = count == 0
+    return rank
+
+
+def non_dominated_sort(x):
+    """src/evox/operators/selection/non_dominate.py:32-115: matrix (:62), column
+    sums (:63), peel (:74-113).  Returns int32 ranks starting at 0."""
+    x = np.asarray(x)
+    dom = dominate_relation(x, x)
+    return rank_from_domination_matrix(dom, dom.sum(axis=0))
+
+
+# --------------------------------------------------------------------------- #
+# crowding distance                                      non_dominate.py:118-180
+# --------------------------------------------------------------------------- #
+def crowding_distance(costs, mask=None):
+    """src/evox/operators/selection/non_dominate.py:118-158.
+
+    Per objective: stable lexsort by (valid first, then cost) (:147); sorted
+    costs; range = c[nv-1]-c[0] (:149); every interior *position* of the full-length
+    order gets (c[i+1]-c[i-1])/range (:151); positions 0 and nv-1 get +inf
+    (:152-153); masked rows become -inf (:155); objectives are summed (:158).
+    nv-1 == -1 wraps to the last position exactly as JAX indexing does.
+    """
+    costs = np.asarray(costs, dtype=F32)
+    n = costs.shape[0]
+    if mask is None:
+        nv = n
+        mask = np.ones(n, dtype=bool)
+    else:
+        mask = np.asarray(mask, dtype=bool)
+        nv = int(mask.sum())
+    total = np.zeros(n, dtype=F32)
+    if n == 0:
+        return total
+    with np.errstate(invalid="ignore", divide="ignore"):
+        for k in range(costs.shape[1]):
+            c = costs[:, k]
+            order = np.lexsort((c, ~mask))
+            cs = c[order]
+            rng = F32(cs[nv - 1] - cs[0])
+            d = np.zeros(n, dtype=F32)                      # jnp.empty -> zeros
+            d[order[1:-1]] = (cs[2:] - cs[:-2]) / rng
+            d[order[0]] = np.inf
+            d[order[nv - 1]] = np.inf
+            d = np.where(mask, d, F32(-np.inf)).astype(F32)
+            total = (total + d).astype(F32) if k else d
+    return total
+
+
+def crowding_distance_sort(x, mask=None):
+    """src/evox/operators/selection/non_dominate.py:161-180: stable ascending argsort."""
+    return np.argsort(crowding_distance(x, mask), kind="stable").astype(np.int32)
+
+
+# --------------------------------------------------------------------------- #
+# survivor selection                                     non_dominate.py:183-232
+# --------------------------------------------------------------------------- #
+def non_dominate(population, fitness, topk, deduplicate=False):
+    """src/evox/operators/selection/non_dominate.py:183-222.
+
+    Keeps the reference's quirk: :216 stores the crowding *argsort permutation* and
+    :218 uses its negation as the secondary sort key.  The dedupe branch (:188-208)
+    follows jnp.unique(size=N) of jax 0.4.x (index pad = first sorted row); that
+    padding rule belongs to jaxlib and is not pinned by any reference test.
+    """
+    population = np.asarray(population)
+    fitness = np.asarray(fitness, dtype=F32)
+    fitness_bak = fitness
+    if deduplicate:
+        n = population.shape[0]
+        _, uidx, ucnt = np.unique(population, axis=0, return_index=True, return_counts=True)
+        count = uidx.shape[0]
+        pad = n - count
+        uidx = np.concatenate([uidx, np.repeat(uidx[:1], pad)])
+        population = population[uidx]
+        fitness = fitness[uidx]
+        fitness_bak = fitness
+        fitness = np.where((np.arange(n) < count)[:, None], fitness, F32(np.inf)).astype(F32)
+    rank = non_dominated_sort(fitness)
+    order = np.argsort(rank, kind="stable")
+    worst = rank[order[topk - 1]]
+    mask = rank == worst
+    cd_perm = crowding_distance_sort(fitness, mask)
+    combined = np.lexsort((-cd_perm, rank))[:topk]
+    return population[combined], fitness_bak[combined]
+
+
+# --------------------------------------------------------------------------- #
+# DTLZ                                        problems/numerical/dtlz.py:36-322
+# --------------------------------------------------------------------------- #
+def _shape_linear(scale, X, m):
+    """(scale) * fliplr(cumprod([1, x_0..x_{m-2}])) * [1, 1-x_{m-2}, ..., 1-x_0]   dtlz.py:62-67"""
+    n = X.shape[0]
+    cp = np.cumprod(np.c_[np.ones((n, 1), F32), X[:, :m - 1]], axis=1, dtype=F32)
+    return (scale * np.fliplr(cp) * np.c_[np.ones((n, 1), F32), 1 - X[:, m - 2::-1]]).astype(F32)
+
+
+def _shape_sphere(scale, X, m, clamp=True):
+    """dtlz.py:87-101: cos/sin(x*pi/2) staircase, cos clamped at 0 in DTLZ2-6 (not in LSMOP5-8)."""
+    n = X.shape[0]
+    cs = np.cos(X[:, :m - 1] * np.pi / 2).astype(F32)
+    if clamp:
+        cs = np.maximum(cs, 0)
+    cp = np.cumprod(np.c_[np.ones((n, 1), F32), cs], axis=1, dtype=F32)
+    sn = np.sin(X[:, m - 2::-1] * np.pi / 2).astype(F32)
+    return (scale * np.fliplr(cp) * np.c_[np.ones((n, 1), F32), sn]).astype(F32)
+
+
+def _g_multimodal(X, m):
+    """100*(k + sum((x-.5)^2 - cos(20*pi*(x-.5))))   dtlz.py:52-61, :118-131"""
+    d = X.shape[1]
+    t = X[:, m - 1:] - F32(0.5)
+    s = np.sum(t * t - np.cos(20 * np.pi * t), axis=1, keepdims=True, dtype=F32)
+    return (100 * (d - m + 1 + s)).astype(F32)
+
+
+def _integer_pow_f32(x, y):
+    """lax.integer_pow (what `X.at[...].power(100)` lowers to): square-and-multiply in f32."""
+    acc, base = None, x.astype(F32)
+    while y > 0:
+        if y & 1:
+            acc = base if acc is None else (acc * base).astype(F32)
+        y >>= 1
+        if y:
+            base = (base * base).astype(F32)
+    return acc
+
+
+def dtlz(which, X, m):
+    """DTLZ1..7 evaluate.  dtlz.py:48-69, 84-103, 115-145, 152-172, 188-208, 244-265, 303-322."""
+    X = np.array(X, dtype=F32, copy=True)
+    n, d = X.shape
+    with np.errstate(all="ignore"):
+        if which == 1:
+            g = _g_multimodal(X, m)
+            return _shape_linear(F32(0.5) * (1 + g), X, m)
+        if which == 2:
+            g = np.sum((X[:, m - 1:] - F32(0.5)) ** 2, axis=1, keepdims=True, dtype=F32)
+            return _shape_sphere(1 + g, X, m)
+        if which == 3:
+            g = _g_multimodal(X, m)
+            return _shape_sphere(1 + g, X, m)
+        if which == 4:
+            X[:, :m - 1] = _integer_pow_f32(X[:, :m - 1], 100)
+            g = np.sum((X[:, m - 1:] - F32(0.5)) ** 2, axis=1, keepdims=True, dtype=F32)
+            return _shape_sphere(1 + g, X, m)
+        if which in (5, 6):
+            if which == 5:
+                g = np.sum((X[:, m - 1:] - F32(0.5)) ** 2, axis=1, keepdims=True, dtype=F32)
+            else:
+                g = np.sum(np.power(X[:, m - 1:], F32(0.1)), axis=1, keepdims=True, dtype=F32)
+            X[:, 1:m - 1] = (1 + 2 * g * X[:, 1:m - 1]) / (2 + 2 * g)
+            return _shape_sphere(1 + g, X, m)
+        if which == 7:
+            g = 1 + 9 * np.mean(X[:, m - 1:], axis=1, keepdims=True, dtype=F32)
+            f = np.zeros((n, m), F32)
+            f[:, :m - 1] = X[:, :m - 1]
+            h = m - np.sum(f[:, :m - 1] / (1 + g) * (1 + np.sin(3 * np.pi * f[:, :m - 1])),
+                           axis=1, keepdims=True, dtype=F32)
+            f[:, m - 1:] = (1 + g) * h
+            return f
+    raise ValueError(which)
+
+
+# --------------------------------------------------------------------------- #
+# MaF1                                         problems/numerical/maf.py:95-108
+# --------------------------------------------------------------------------- #
+def maf1(X, m):
+    X = np.asarray(X, dtype=F32)
+    g = np.sum((X[:, m - 1:] - F32(0.5)) ** 2, axis=1, dtype=F32).reshape(-1, 1)
+    rg = 1 + g
+    return (rg - _shape_linear(rg, X, m)).astype(F32)
+
+
+# --------------------------------------------------------------------------- #
+# LSMOP                                       problems/numerical/lsmop.py:17-454
+# --------------------------------------------------------------------------- #
+def lsmop_groups(d, m, nk=5):
+    """Sub-group lengths and offsets.  lsmop.py:46-54: logistic map c_i, then
+    floor(c/sum(c)*d/nk) evaluated in float32, cumulative offsets of sublen*nk."""
+    c = [3.8 * 0.1 * (1 - 0.1)]
+    for _ in range(1, m):
+        c.append(3.8 * c[-1] * (1 - c[-1]))
+    c = np.asarray(c, dtype=F32)
+    sub = np.floor(c / np.sum(c, dtype=F32) * d / nk)
+    sublen = tuple(int(v) for v in sub)
+    off = tuple(int(v) for v in np.r_[0, np.cumsum(sub * nk)])
+    return sublen, off
+
+
+def _sphere(x):                      # sphere.py:5-6
+    return np.sum(x * x, axis=-1, dtype=F32)
+
+
+def _griewank(x):                    # griewank.py:6-12
+    k = np.sqrt(np.arange(1, x.shape[1] + 1, dtype=F32))
+    return (F32(1 / 4000) * np.sum(x * x, axis=1, dtype=F32)
+            - np.prod(np.cos(x / k), axis=1, dtype=F32) + 1).astype(F32)
+
+
+def _rosenbrock(x):                  # rosenbrock.py:6-12
+    a, b = x[:, :-1], x[:, 1:]
+    return np.sum(100 * (b - a * a) ** 2 + (a - 1) ** 2, axis=1, dtype=F32)
+
+
+def _ackley(x, a=20, b=0.2, c=2 * np.pi):   # ackley.py:7-13, defaults lsmop.py:59
+    return (-a * np.exp(-b * np.sqrt(np.mean(x * x, axis=1, dtype=F32)))
+            - np.exp(np.mean(np.cos(c * x), axis=1, dtype=F32)) + a + np.e).astype(F32)
+
+
+def _schwefel(x):                    # lsmop.py:76-77
+    return np.max(np.abs(x), axis=-1)
+
+
+def _rastrigin(x):                   # lsmop.py:84-86
+    return np.sum(x * x - 10 * np.cos(2 * np.pi * x) + 10, axis=1, dtype=F32)
+
+
+_LSMOP_INNER = {          # lsmop.py:136, 161, 188, 215, 240, 277, 309, 348, 386
+    1: (_sphere,), 2: (_griewank, _schwefel), 3: (_rastrigin, _rosenbrock),
+    4: (_ackley, _griewank), 5: (_sphere,), 6: (_rosenbrock, _schwefel),
+    7: (_ackley, _rosenbrock), 8: (_griewank, _sphere), 9: (_sphere, _ackley),
+}
+
+
+def lsmop(which, X, m, sublen=None, off=None, nk=5):
+    """LSMOP1..9 evaluate (lsmop.py:127-141 ... 400-426) with `_calc_g` (:88-111).
+
+    `sublen`/`off` default to the groups of d = X.shape[1]; pass the constructor's
+    to reproduce the reference's d=None quirk (groups sized for d=100*m)."""
+    X = np.array(X, dtype=F32, copy=True)
+    n, d = X.shape
+    if sublen is None:
+        sublen, off = lsmop_groups(d, m, nk)
+    with np.errstate(all="ignore"):
+        j = np.arange(m, d + 1, dtype=F32) / F32(d)
+        w = 1 + j if which <= 4 else 1 + np.cos(j * np.pi / 2).astype(F32)
+        X[:, m - 1:d] = w * X[:, m - 1:d] - X[:, :1] * 10
+        g = []
+        for o, sl, fn in zip(off, sublen, cycle(_LSMOP_INNER[which])):
+            acc = None
+            for b in range(nk):
+                s = o + m - 1 + b * sl
+                r = fn(X[:, s:s + sl]).astype(F32)
+                acc = r if acc is None else (acc + r).astype(F32)
+            g.append(acc)
+        g = np.stack(g, axis=1)
+        g = (g / np.asarray(sublen, dtype=F32)[None, :] / nk).astype(F32)
+        if which <= 4:
+            return _shape_linear(1 + g, X, m)
+        if which <= 8:
+            return _shape_sphere(1 + g + np.c_[g[:, 1:], np.zeros((n, 1), F32)], X, m, clamp=False)
+        gs = 1 + np.sum(g, axis=1, keepdims=True, dtype=F32)
+        f = np.zeros((n, m), F32)
+        f[:, :m - 1] = X[:, :m - 1]
+        h = m - np.sum(f[:, :m - 1] / (1 + gs) * (1 + np.sin(3 * np.pi * f[:, :m - 1])),
+                       axis=1, keepdims=True, dtype=F32)
+        f[:, m - 1:m] = (1 + gs) * h
+        return f
