@@ -1,0 +1,49 @@
+"""Builds evox_b200/libevoxmo.so from csrc/*.cu with nvcc for sm_100a (in-tree, no JIT cache)."""
+import os
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+from pathlib import Path
+
+HERE = Path(__file__).resolve().parent
+CSRC = HERE / "csrc"
+OUT = HERE / "libevoxmo.so"
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+         "-Xcompiler", "-fPIC", "-diag-suppress", "177"]
+
+
+def _stale(obj, deps):
+    return (not obj.exists()) or any(obj.stat().st_mtime < d.stat().st_mtime for d in deps)
+
+
+def build(verbose=False, force=False):
+    srcs = sorted(CSRC.glob("*.cu"))
+    hdrs = sorted(CSRC.glob("*.cuh")) + [HERE.parent / "include" / "evoxmo.h"]
+    objdir = HERE / "build"
+    objdir.mkdir(exist_ok=True)
+
+    def one(src):
+        obj = objdir / (src.stem + ".o")
+        if force or _stale(obj, [src] + hdrs):
+            cmd = [NVCC, *FLAGS, "-c", str(src), "-o", str(obj)] + (["-Xptxas", "-v"] if verbose else [])
+            r = subprocess.run(cmd, capture_output=True, text=True)
+            if r.returncode != 0:
+                raise RuntimeError(f"nvcc failed for {src.name}:\n{r.stdout}\n{r.stderr}")
+            if verbose:
+                sys.stderr.write(r.stderr)
+        return obj
+
+    with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
+        objs = list(ex.map(one, srcs))
+    if force or _stale(OUT, objs):
+        r = subprocess.run([NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", str(OUT), *map(str, objs),
+                            "-lcudart"],
+                           capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    return OUT
+
+
+if __name__ == "__main__":
+    print(build(verbose="-v" in sys.argv, force="-f" in sys.argv))

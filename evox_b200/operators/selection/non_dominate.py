@@ -1,0 +1,134 @@
+"""Mirror of `evox.operators.selection.non_dominate` (src/evox/operators/selection/non_dominate.py).
+
+Same names, argument meaning and results as the reference; arrays are CUDA tensors and the work is
+done by libevoxmo.so.  `method` is accepted for drop-in compatibility: the reference's three
+methods ("scan", "full map-reduce", "host", :49-60) are three ways of evaluating the same ranks, and
+all of them map to the one CUDA implementation.
+"""
+import torch
+
+from ..._dev import as_f32_cuda, stream_ptr, workspace
+from ..._lib import check, lib
+
+_METHODS = ("auto", "scan", "full map-reduce", "host")
+
+
+def non_dominated_sort(x, method="auto"):
+    """Front index (int32, from 0) of every row of x [n, m].  non_dominate.py:32-115."""
+    assert method in _METHODS, "method must be either 'auto', 'scan', or 'full map-reduce', 'host'"
+    x = as_f32_cuda(x, "x")
+    if x.dim() != 2:
+        raise ValueError(f"non_dominated_sort: expected [n, m], got {tuple(x.shape)}")
+    n, m = x.shape
+    rank = torch.empty((n,), dtype=torch.int32, device="cuda")
+    if n == 0:
+        return rank
+    L = lib()
+    nbytes = L.evx_nds_workspace_bytes(n, m)
+    if nbytes == 0:
+        raise ValueError(f"non_dominated_sort: unsupported shape n={n}, m={m}")
+    ws = workspace(nbytes, "nds")
+    check(L.evx_nds_f32(x.data_ptr(), n, m, rank.data_ptr(), ws.data_ptr(), ws.numel(), stream_ptr()))
+    return rank
+
+
+def host_rank_from_domination_matrix(dominate_mat, dominate_count):
+    """non_dominate.py:13-29 on the device: ranks from a dense bool matrix and its column sums."""
+    d = dominate_mat if isinstance(dominate_mat, torch.Tensor) else torch.as_tensor(dominate_mat)
+    d = d.to(device="cuda", dtype=torch.uint8).contiguous()
+    n = d.shape[0]
+    cnt = None
+    if dominate_count is not None:
+        cnt = (dominate_count if isinstance(dominate_count, torch.Tensor) else torch.as_tensor(dominate_count))
+        cnt = cnt.to(device="cuda", dtype=torch.int32).contiguous()
+    rank = torch.empty((n,), dtype=torch.int32, device="cuda")
+    if n == 0:
+        return rank
+    L = lib()
+    ws = workspace(L.evx_rank_from_matrix_workspace_bytes(n), "dense")
+    check(L.evx_rank_from_matrix_u8(d.data_ptr(), None if cnt is None else cnt.data_ptr(), n, rank.data_ptr(),
+                                    ws.data_ptr(), ws.numel(), stream_ptr()))
+    return rank
+
+
+def _mask_u8(mask, n):
+    if mask is None:
+        return None
+    mk = mask if isinstance(mask, torch.Tensor) else torch.as_tensor(mask)
+    if mk.shape != (n,):
+        raise ValueError(f"mask: expected shape ({n},), got {tuple(mk.shape)}")
+    return mk.to(device="cuda").ne(0).to(torch.uint8).contiguous()
+
+
+def crowding_distance(costs, mask=None):
+    """Crowding distance of costs [n, m]; rows with mask False get -inf.  non_dominate.py:118-158."""
+    c = as_f32_cuda(costs, "costs")
+    n, m = c.shape
+    out = torch.empty((n,), dtype=torch.float32, device="cuda")
+    if n == 0:
+        return out
+    mk = _mask_u8(mask, n)
+    L = lib()
+    ws = workspace(L.evx_crowding_workspace_bytes(n, m), "cd")
+    check(L.evx_crowding_distance_f32(c.data_ptr(), None if mk is None else mk.data_ptr(), n, m, out.data_ptr(),
+                                      ws.data_ptr(), ws.numel(), stream_ptr()))
+    return out
+
+
+def crowding_distance_sort(x, mask=None):
+    """Stable ascending argsort of `crowding_distance(x, mask)`.  non_dominate.py:161-180."""
+    c = as_f32_cuda(x, "x")
+    n, m = c.shape
+    out = torch.empty((n,), dtype=torch.int32, device="cuda")
+    if n == 0:
+        return out
+    mk = _mask_u8(mask, n)
+    L = lib()
+    ws = workspace(L.evx_crowding_workspace_bytes(n, m), "cd")
+    check(L.evx_crowding_distance_sort_f32(c.data_ptr(), None if mk is None else mk.data_ptr(), n, m, out.data_ptr(),
+                                           ws.data_ptr(), ws.numel(), stream_ptr()))
+    return out
+
+
+def _lexsort2(secondary, primary):
+    """np.lexsort((secondary, primary)): stable sort by primary, ties by secondary."""
+    o = torch.sort(secondary, stable=True).indices
+    return o[torch.sort(primary[o], stable=True).indices]
+
+
+def non_dominate(population, fitness, topk, deduplicate):
+    """Survivor selection.  non_dominate.py:183-222; the host glue (argsort / lexsort / gather) is
+    torch here where it is jnp in the reference, and keeps the reference's :216/:218 key choice: the
+    secondary key is the negated crowding *argsort permutation*."""
+    pop = population if isinstance(population, torch.Tensor) else torch.as_tensor(population)
+    pop = pop.to("cuda")
+    fit = as_f32_cuda(fitness, "fitness")
+    fit_bak = fit
+    if deduplicate:
+        n = pop.shape[0]
+        uniq, inverse = torch.unique(pop, dim=0, return_inverse=True)
+        count = uniq.shape[0]
+        ar = torch.arange(n, device="cuda")
+        first = torch.full((count,), n, dtype=torch.long, device="cuda").scatter_reduce(0, inverse, ar, "amin")
+        uidx = torch.cat([first, first[:1].expand(n - count)])          # jnp.unique(size=n) index padding
+        pop, fit = pop[uidx], fit[uidx]
+        fit_bak = fit
+        fit = torch.where((ar < count)[:, None], fit, torch.full_like(fit, float("inf")))
+    rank = non_dominated_sort(fit)
+    order = torch.sort(rank, stable=True).indices
+    worst = rank[order[topk - 1]]
+    mask = rank == worst
+    cd_perm = crowding_distance_sort(fit, mask)
+    combined = _lexsort2(-cd_perm, rank)[:topk]
+    return pop[combined], fit_bak[combined]
+
+
+class NonDominate:
+    """non_dominate.py:225-232."""
+
+    def __init__(self, topk, deduplicate=False):
+        self.topk = topk
+        self.deduplicate = deduplicate
+
+    def __call__(self, population, fitness):
+        return non_dominate(population, fitness, self.topk, self.deduplicate)

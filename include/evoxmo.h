@@ -1,0 +1,141 @@
+/* evoxmo.h - C ABI of libevoxmo.so: EvoX's multi-objective environmental-selection hot path
+ * (dominance, non-dominated sort, crowding distance, DTLZ/LSMOP/MaF1 evaluate) as hand-written
+ * CUDA for sm_100a (B200).
+ *
+ * Conventions
+ *   - Every pointer marked "device" is a CUDA device pointer owned by the caller (XLA, torch, ...);
+ *     the library never frees or retains it.  Inputs are read-only.  Arrays are row-major,
+ *     float32 / int32 / uint8 exactly as the reference holds them (x64 is never enabled there).
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  All work is
+ *     enqueued on it.  Functions documented "synchronises" block the host on that stream.
+ *   - Scratch memory comes from the caller: ask `*_workspace_bytes`, pass `ws`/`ws_bytes`
+ *     (device, 256-byte aligned).  The `*_host_*` entry points take HOST buffers and use a
+ *     grow-only per-device arena owned by the library instead.
+ *   - Return value: 0 on success, non-zero on failure; `evx_last_error()` returns a
+ *     thread-local message.  No C++ exception, abort or exit crosses this boundary.
+ *   - Reference citations are paths under the EvoX source tree (src/evox/...).
+ */
+#ifndef EVOXMO_H_
+#define EVOXMO_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EVX_OK 0
+#define EVX_ERR_ARG 1        /* bad shape / null pointer / unsupported m                 */
+#define EVX_ERR_WORKSPACE 2  /* workspace missing, misaligned or too small               */
+#define EVX_ERR_CUDA 3       /* a CUDA runtime call or kernel failed                     */
+#define EVX_ERR_NOMEM 4      /* arena allocation failed (host entry points)              */
+
+#define EVX_MAX_OBJECTIVES 32
+
+int evx_version(void);
+const char* evx_last_error(void);
+
+/* ---- (a1) dominance relation ------------------------------------------------------------------
+ * replaces utils/common.py:88-97  `dominate_relation(x, y)`:
+ *   out[i, j] = all_k(x[i,k] <= y[j,k]) && any_k(x[i,k] < y[j,k]),  IEEE compares (NaN -> false).
+ * x: device float32 [nx, m], y: device float32 [ny, m].
+ * _u8  : out device uint8  [nx, ny]           (the reference's bool matrix, 1 byte per pair)
+ * _bits: out device uint32 [nx, ceil(ny/32)]  (bit j%32 of word j/32 = pair (i,j); tail bits 0)   */
+int evx_dominate_relation_u8(const float* x, int64_t nx, const float* y, int64_t ny, int32_t m,
+                             uint8_t* out, void* stream);
+int evx_dominate_relation_bits(const float* x, int64_t nx, const float* y, int64_t ny, int32_t m,
+                               uint32_t* out, void* stream);
+
+/* ---- (a2) non-dominated sort ------------------------------------------------------------------
+ * replaces operators/selection/non_dominate.py:32-115  `non_dominated_sort(x, method)`
+ * (all three `method`s compute the same ranks; this is the one implementation behind them).
+ * x: device float32 [n, m];  rank: device int32 [n], front index starting at 0, bit-exact.
+ * Synchronises (the number of fronts is data dependent, non_dominate.py:78-80).                    */
+size_t evx_nds_workspace_bytes(int64_t n, int32_t m);
+int evx_nds_f32(const float* x, int64_t n, int32_t m, int32_t* rank, void* ws, size_t ws_bytes,
+                void* stream);
+/* Same, host buffers in and out (H2D + D2H inside; library arena for scratch).                    */
+int evx_nds_host_f32(const float* x_host, int64_t n, int32_t m, int32_t* rank_host);
+/* Number of fronts found by the last evx_nds_* call on this host thread.                          */
+int32_t evx_nds_last_num_fronts(void);
+
+/* ---- (a3) rank from a dense domination matrix ------------------------------------------------
+ * replaces operators/selection/non_dominate.py:13-29  `host_rank_from_domination_matrix`
+ * (the `method="host"` pure_callback, :65-72), on the device.
+ * dom: device uint8 [n, n] (dom[i,j] != 0: i dominates j); count: device int32 [n] column sums, or
+ * NULL to have them computed.  rank: device int32 [n].  Synchronises.                              */
+size_t evx_rank_from_matrix_workspace_bytes(int64_t n);
+int evx_rank_from_matrix_u8(const uint8_t* dom, const int32_t* count, int64_t n, int32_t* rank,
+                            void* ws, size_t ws_bytes, void* stream);
+
+/* ---- (a4, a5) crowding distance ---------------------------------------------------------------
+ * replaces operators/selection/non_dominate.py:118-158 `crowding_distance(costs, mask)` and
+ * :161-180 `crowding_distance_sort(x, mask)`.
+ * costs: device float32 [n, m]; mask: device uint8 [n] (non-zero = participates) or NULL (all).
+ * dist: device float32 [n] (+inf boundaries, -inf masked rows, exact);
+ * order: device int32 [n] = stable ascending argsort of dist (NaN last).  Asynchronous.            */
+size_t evx_crowding_workspace_bytes(int64_t n, int32_t m);
+int evx_crowding_distance_f32(const float* costs, const uint8_t* mask, int64_t n, int32_t m,
+                              float* dist, void* ws, size_t ws_bytes, void* stream);
+int evx_crowding_distance_sort_f32(const float* costs, const uint8_t* mask, int64_t n, int32_t m,
+                                   int32_t* order, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- (a7) DTLZ1..7 evaluate -------------------------------------------------------------------
+ * replaces problems/numerical/dtlz.py:48-69, 84-103, 115-145, 152-172, 188-208, 244-265, 303-322
+ * `DTLZk.evaluate(state, X)`.  X: device float32 [n, d]; F: device float32 [n, m].  Asynchronous. */
+int evx_eval_dtlz_f32(int32_t which, const float* X, int64_t n, int32_t d, int32_t m, float* F,
+                      void* stream);
+
+/* ---- (a9) MaF1 evaluate -----------------------------------------------------------------------
+ * replaces problems/numerical/maf.py:95-108 `MaF1.evaluate`.                                      */
+int evx_eval_maf1_f32(const float* X, int64_t n, int32_t d, int32_t m, float* F, void* stream);
+
+/* ---- (a8) LSMOP1..9 evaluate ------------------------------------------------------------------
+ * replaces problems/numerical/lsmop.py:127-141 ... 400-426 `LSMOPk.evaluate` with `_calc_g`
+ * (:88-111).  sublen: HOST int32 [m] and off: HOST int32 [m+1] are the constructor's group lengths
+ * and offsets (lsmop.py:46-54; `evx_lsmop_groups` computes them the same way, in float32).        */
+int evx_lsmop_groups(int32_t d, int32_t m, int32_t* sublen_host, int32_t* off_host);
+int evx_eval_lsmop_f32(int32_t which, const float* X, int64_t n, int32_t d, int32_t m,
+                       const int32_t* sublen_host, const int32_t* off_host, float* F, void* stream);
+
+/* ---- sharded non-dominated sort (one process per GPU; column panels dealt round-robin) --------
+ * The exchange step between ranks - all-gather of each front's membership - is done by the caller
+ * (torch.distributed / NCCL) between these calls; see INTEGRATION.md.  No reference counterpart:
+ * the reference replicates selection on every device (workflows/std_workflow.py:160,187-200).     */
+typedef struct evx_nds_shard evx_nds_shard;   /* opaque plan living in host memory                 */
+size_t evx_nds_shard_workspace_bytes(int64_t n, int32_t m, int32_t world, int32_t rank);
+evx_nds_shard* evx_nds_shard_create(int64_t n, int32_t m, int32_t world, int32_t rank, void* ws,
+                                    size_t ws_bytes);
+void evx_nds_shard_destroy(evx_nds_shard* p);
+/* sort + unique + this rank's panels of the bit matrix + their column counts (asynchronous)       */
+int evx_nds_shard_build(evx_nds_shard* p, const float* x, void* stream);
+/* number of uint32 words each rank contributes to the per-front membership mask                   */
+int64_t evx_nds_shard_mask_words(const evx_nds_shard* p);
+/* detect this rank's members of front k -> local_mask (device, mask_words); asynchronous          */
+int evx_nds_shard_detect(evx_nds_shard* p, int32_t k, uint32_t* local_mask, void* stream);
+/* apply the all-gathered masks (device, world*mask_words, rank-major) of front k to this rank's
+ * counts; `any_out` (device int32) is set non-zero if the front was non-empty; asynchronous       */
+int evx_nds_shard_apply(evx_nds_shard* p, int32_t k, const uint32_t* all_masks, int32_t* any_out,
+                        void* stream);
+/* ranks of the columns this rank owns, scattered to original row order into rank_partial (device
+ * int32 [n], zero elsewhere: a SUM all-reduce over ranks yields the final ranks); asynchronous    */
+int evx_nds_shard_ranks(evx_nds_shard* p, int32_t* rank_partial, void* stream);
+
+/* ---- instrumentation --------------------------------------------------------------------------
+ * kernels launched by this library on this host thread since the last reset (bench.py reports it) */
+int64_t evx_launch_count(void);
+void evx_launch_count_reset(void);
+/* per-stage device times (CUDA events on the call's stream) of the last evx_nds_f32 call made on
+ * this host thread while enabled: sort+unique, dominance tile kernel, front peeling.              */
+void evx_profile_enable(int32_t on);
+int evx_profile_last(float* prep_ms, float* tiles_ms, float* peel_ms);
+/* register-only issue-rate probe: runs `iters` dependent-free compare+logic steps per thread on
+ * the whole chip and returns the measured pair-tests per second for the inner step the dominance
+ * tile kernel uses (the denominator of the compare roofline).  Synchronises.                      */
+int evx_probe_compare_rate(int32_t m, int64_t iters, double* pairs_per_s, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EVOXMO_H_ */
