@@ -18,8 +18,12 @@
 //   5. Peeling: front k = columns whose count is 0.  Every front row is read exactly once per
 //      panel (128 B line), rows are summed bit-sliced (carry-save adders), and the per-column sums
 //      are subtracted from the counts.  Total peel traffic = the matrix, once.
+#include <cooperative_groups.h>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
+
+#include <cstdlib>
+#include <cstring>
 
 #include "common.cuh"
 
@@ -39,13 +43,17 @@ struct Scal {
     int n_nan;      // rows holding a NaN
     int nf[2];      // size of the current front list, double buffered by front parity
     int any[ANY_SLOTS];
+    int nf3[3];     // persistent peel: front sizes, triple buffered (read k, append k+1, clear k+2)
+    int fronts;     // persistent peel: number of fronts found
+    unsigned int barrier;   // persistent peel: grid barrier arrivals (monotonic)
 };
 
 struct Layout {
     int64_t n, npad;
     int m, world, rank, np, npl, npl_max;
     size_t keys, idxA, idxB, skeyA, skeyB, flags, incl, cubtmp, cubtmp_bytes, ucols, row2u, count,
-        rank_u, flist, mask, scal, bits, total;
+        rank_u, flist, flist2, cplanes, mask, scal, bits, total, tcols, bkeyA, bkeyB, label;
+    int kplanes;
     int64_t bits_words;
 };
 
@@ -58,11 +66,14 @@ __device__ __forceinline__ int64_t d_panel_words_before(int64_t l, int world, in
 }
 
 static size_t cub_temp_bytes(int64_t n) {
-    size_t a = 0, b = 0;
+    size_t a = 0, b = 0, c = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, c, (const uint64_t*)nullptr, (uint64_t*)nullptr,
+                                    (const int*)nullptr, (int*)nullptr, (int)n);
     cub::DeviceRadixSort::SortPairs(nullptr, a, (const uint32_t*)nullptr, (uint32_t*)nullptr,
                                     (const int*)nullptr, (int*)nullptr, (int)n);
     cub::DeviceScan::InclusiveSum(nullptr, b, (const int*)nullptr, (int*)nullptr, (int)n);
-    return a > b ? a : b;
+    a = a > b ? a : b;
+    return a > c ? a : c;
 }
 
 static Layout make_layout(int64_t n, int m, int world, int rank) {
@@ -84,11 +95,19 @@ static Layout make_layout(int64_t n, int m, int world, int rank) {
     L.incl = take(sizeof(int) * n);
     L.cubtmp_bytes = cub_temp_bytes(n);
     L.cubtmp = take(L.cubtmp_bytes);
-    L.ucols = take(sizeof(float) * (size_t)(m > 1 ? m - 1 : 1) * L.npad);
+    L.ucols = take(sizeof(float) * (size_t)m * L.npad);
+    L.tcols = take(sizeof(float) * (size_t)m * L.npad);
+    L.bkeyA = take(sizeof(uint64_t) * n);
+    L.bkeyB = take(sizeof(uint64_t) * n);
+    L.label = take(sizeof(int) * n);
     L.row2u = take(sizeof(int) * n);
     L.count = take(sizeof(int) * (size_t)L.npl_max * TW);
     L.rank_u = take(sizeof(int) * (size_t)L.npl_max * TW);
     L.flist = take(sizeof(int) * L.npad);
+    L.flist2 = take(sizeof(int) * L.npad);
+    L.kplanes = 1;
+    while ((1ll << L.kplanes) <= L.npad) ++L.kplanes;          // counts < npad fit in kplanes bits
+    L.cplanes = take(sizeof(uint32_t) * (size_t)L.npl_max * (L.kplanes + 1) * PW);
     L.mask = take(sizeof(uint32_t) * (size_t)L.npl_max * PW * world);
     L.scal = take(sizeof(Scal));
     L.bits_words = panel_words_before(L.npl, world, rank);
@@ -136,7 +155,7 @@ __global__ void k_mark_heads(const uint32_t* __restrict__ keys, const int* __res
 
 __global__ void k_scatter_unique(const float* __restrict__ x, const int* __restrict__ idx,
                                  const int* __restrict__ incl, const int* __restrict__ flags, int64_t n, int m,
-                                 int64_t npad, Scal* scal, float* __restrict__ ucols, int* __restrict__ row2u) {
+                                 int64_t npad, Scal* scal, float* __restrict__ tcols, int* __restrict__ row2u) {
     int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
     const int64_t nvalid = n - scal->n_nan;
@@ -145,9 +164,45 @@ __global__ void k_scatter_unique(const float* __restrict__ x, const int* __restr
     const int u = incl[p] - 1;
     row2u[row] = u;
     if (flags[p]) {
-        for (int k = 1; k < m; ++k) ucols[(int64_t)(k - 1) * npad + u] = x[(int64_t)row * m + k] + 0.0f;
+        for (int k = 0; k < m; ++k) tcols[(int64_t)k * npad + u] = x[(int64_t)row * m + k] + 0.0f;
     }
     if (p == nvalid - 1) scal->U = u + 1;
+}
+
+// ------------------------------------------------------------------------------------------------
+// stage 1b: block-local re-labelling
+// ------------------------------------------------------------------------------------------------
+// Unique rows are cut into blocks of TW consecutive lexicographic positions, and inside each block
+// they are re-ordered by f1.  Between different blocks the lexicographic order still decides f0
+// (lower block => f0 <=), so off-diagonal tiles test objectives 1..M-1 only; and because both the
+// rows of a warp's slab and the 32 columns of a word are now contiguous in f1, whole (slab, word)
+// sub-tiles are decided by one compare of their f1 ranges: all-fail (skipped) or all-pass on f1
+// (one objective fewer).  Inside a block either direction may dominate: diagonal tiles test all M.
+__global__ void k_block_keys(const float* __restrict__ tcols, int64_t n, int64_t npad, int m, int np,
+                             const Scal* __restrict__ scal, uint64_t* __restrict__ keys, int* __restrict__ vals) {
+    const int64_t u = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (u >= n) return;
+    const bool valid = u < scal->U;
+    const uint32_t f1 = (valid && m > 1) ? float_key(tcols[npad + u]) : 0u;
+    keys[u] = valid ? (((uint64_t)(u / TW) << 32) | f1) : ((uint64_t)np << 32);     // invalid: past every block
+    vals[u] = (int)u;
+}
+
+__global__ void k_block_permute(const float* __restrict__ tcols, const int* __restrict__ perm, int64_t n,
+                                int64_t npad, int m, const Scal* __restrict__ scal, float* __restrict__ ucols,
+                                int* __restrict__ label_of_u) {
+    const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= n || v >= scal->U) return;
+    const int u = perm[v];
+    label_of_u[u] = (int)v;
+    for (int k = 0; k < m; ++k) ucols[(int64_t)k * npad + v] = tcols[(int64_t)k * npad + u];
+}
+
+__global__ void k_relabel_rows(int* __restrict__ row2u, const int* __restrict__ label_of_u, int64_t n) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int u = row2u[i];
+    if (u >= 0) row2u[i] = label_of_u[u];
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -159,25 +214,49 @@ __device__ __forceinline__ void csa(uint32_t& hi, uint32_t& lo, uint32_t a, uint
     lo = u ^ c;
 }
 
-template <int MM>
-__device__ __forceinline__ void load_col(const float* p, float (&v)[MM > 0 ? MM : 1]) {
-    if constexpr (MM == 0) {
-        v[0] = 0.f;
-    } else if constexpr (MM % 4 == 0) {
+template <int C>
+__device__ __forceinline__ void load_col(const float* p, float (&v)[C]) {
+    if constexpr (C % 4 == 0) {
 #pragma unroll
-        for (int t = 0; t < MM / 4; ++t) {
+        for (int t = 0; t < C / 4; ++t) {
             float4 q = reinterpret_cast<const float4*>(p)[t];
             v[4 * t] = q.x; v[4 * t + 1] = q.y; v[4 * t + 2] = q.z; v[4 * t + 3] = q.w;
         }
-    } else if constexpr (MM % 2 == 0) {
+    } else if constexpr (C % 2 == 0) {
 #pragma unroll
-        for (int t = 0; t < MM / 2; ++t) {
+        for (int t = 0; t < C / 2; ++t) {
             float2 q = reinterpret_cast<const float2*>(p)[t];
             v[2 * t] = q.x; v[2 * t + 1] = q.y;
         }
     } else {
 #pragma unroll
-        for (int t = 0; t < MM; ++t) v[t] = p[t];
+        for (int t = 0; t < C; ++t) v[t] = p[t];
+    }
+}
+
+// 32 columns x RB rows per lane; objectives [K0, C) of the staged values take part.
+// The compare runs on the FMA pipe: for finite or infinite a, b (no NaN reaches here)
+//     a <= b   <=>   sign(b - a) == 0
+// (b - a is exactly signed: it rounds to zero only when a == b, and inf - inf gives the canonical
+// positive NaN, i.e. "pass", which is what inf <= inf says).  The fail bits of the objectives are
+// OR-ed (LOP3) and shifted into the word with one funnel shift (SHF): 2 FADD on the FMA pipe and
+// 2 ALU-pipe instructions per 32 pair tests at M = 3, instead of 3 ALU-pipe FSETP/SEL.
+template <int C, int K0>
+__device__ __forceinline__ void word_sign(const float* cp, const float (&xi)[RB][C], uint32_t (&w)[RB]) {
+#pragma unroll
+    for (int q = 0; q < RB; ++q) w[q] = 0u;
+    if constexpr (K0 >= C) return;                    // nothing left to test: every pair passes
+#pragma unroll
+    for (int b = 31; b >= 0; --b) {
+        float cv[C];
+        load_col<C>(cp + b * C, cv);
+#pragma unroll
+        for (int q = 0; q < RB; ++q) {
+            uint32_t f = 0u;
+#pragma unroll
+            for (int k = K0; k < C; ++k) f |= __float_as_uint(cv[k] - xi[q][k]);
+            w[q] = __funnelshift_l(f, w[q], 1);       // (w << 1) | sign(f)
+        }
     }
 }
 
@@ -186,28 +265,23 @@ __device__ __forceinline__ void load_col(const float* p, float (&v)[MM > 0 ? MM 
 // step; each lane assembles its own 32-bit words.  Words are staged through shared memory so the
 // 128-byte panel rows leave as full coalesced lines, and the same pass over the staged words feeds
 // carry-save adders that produce the column counts.
-template <int MM>
-__global__ void __launch_bounds__(TILE_WARPS * 32)
-k_dominance_tiles(const float* __restrict__ ucols, int64_t npad, const Scal* __restrict__ scal,
-                  uint32_t* __restrict__ bits, int* __restrict__ count, int world, int rank) {
-    const int l = blockIdx.y;
-    const int J = l * world + rank;
-    const int U = scal->U;
-    const int col0 = J * TW;
-    if (col0 >= U) return;
-    const int rowlimit = min((J + 1) * TW, U);
-    const int row0 = blockIdx.x * CTA_ROWS;
-    if (row0 >= rowlimit) return;
-
-    extern __shared__ __align__(16) uint32_t smem[];
-    float* colv = reinterpret_cast<float*>(smem);                       // [TW][MM]
-    uint32_t* stage = smem + (MM > 0 ? MM : 0) * TW;                    // [TILE_WARPS][PW][SLAB+1]
+// M = objectives.  Off-diagonal CTAs stage objectives 1..M-1 (C = M-1 values per point), the
+// diagonal CTAs of a panel stage all M.
+template <int M, bool DIAG>
+__device__ __forceinline__ void tile_body(const float* __restrict__ ucols, int64_t npad, int U, int l, int J,
+                                          int col0, int row0, int rowlimit, uint32_t* __restrict__ bits,
+                                          int* __restrict__ count, int world, int rank, uint32_t* smem) {
+    constexpr int C = DIAG ? M : (M > 1 ? M - 1 : 1);      // staged values per point
+    constexpr int KOFF = DIAG ? 0 : 1;                     // first staged objective
+    constexpr bool HAVE = DIAG || M > 1;                   // any objective staged at all
+    float* colv = reinterpret_cast<float*>(smem);                          // [TW][C]
+    uint32_t* stage = smem + M * TW;                                       // [TILE_WARPS][PW][SLAB+1]
     int* scount = reinterpret_cast<int*>(stage + TILE_WARPS * PW * (SLAB + 1));   // [TW]
 
-    if constexpr (MM > 0) {
-        for (int t = threadIdx.x; t < MM * TW; t += blockDim.x) {
-            const int c = t / MM, k = t - c * MM;
-            colv[t] = ucols[(int64_t)k * npad + col0 + c];
+    if constexpr (HAVE) {
+        for (int t = threadIdx.x; t < C * TW; t += blockDim.x) {
+            const int c = t / C, k = t - c * C;
+            colv[t] = ucols[(int64_t)(k + KOFF) * npad + col0 + c];
         }
     }
     for (int t = threadIdx.x; t < TW; t += blockDim.x) scount[t] = 0;
@@ -216,49 +290,71 @@ k_dominance_tiles(const float* __restrict__ ucols, int64_t npad, const Scal* __r
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int rs = row0 + warp * SLAB;                                  // first row of this warp's slab
     if (rs < rowlimit) {
-        float xi[RB][MM > 0 ? MM : 1];
+        float xi[RB][C];
 #pragma unroll
         for (int q = 0; q < RB; ++q)
 #pragma unroll
-            for (int k = 0; k < MM; ++k) xi[q][k] = ucols[(int64_t)k * npad + rs + q * 32 + lane];
+            for (int k = 0; k < C; ++k)
+                xi[q][k] = HAVE ? ucols[(int64_t)(k + KOFF) * npad + rs + q * 32 + lane] : 0.0f;
+        // f1 range of the slab (rows are f1-sorted inside their block): first and last valid row
+        float rmin = 0.f, rmax = 0.f;
+        if constexpr (!DIAG && M > 1) {
+            const int last = min(rs + SLAB, rowlimit) - 1 - rs;             // >= 0
+            rmin = __shfl_sync(0xFFFFFFFFu, xi[0][0], 0);
+            float cand = xi[0][0];
+#pragma unroll
+            for (int q = 1; q < RB; ++q) cand = ((last >> 5) == q) ? xi[q][0] : cand;
+            rmax = __shfl_sync(0xFFFFFFFFu, cand, last & 31);
+        }
 
         uint32_t* st = stage + warp * PW * (SLAB + 1);
         for (int wc = 0; wc < PW; ++wc) {
             const int cb = col0 + wc * 32;                              // first column of this word
             uint32_t w[RB];
+            const float* cp = colv + wc * 32 * C;
+            const int ncol = min(32, U - cb);                           // valid columns in this word
+            if (ncol <= 0) {
 #pragma unroll
-            for (int q = 0; q < RB; ++q) w[q] = 0u;
-            if (cb + 31 > rs) {                                         // else wholly on/below the diagonal
-                const float* cp = colv + wc * 32 * MM;
+                for (int q = 0; q < RB; ++q) w[q] = 0u;
+            } else {
+                if constexpr (DIAG) {
 #pragma unroll
-                for (int b = 0; b < 32; ++b) {
-                    float cv[MM > 0 ? MM : 1];
-                    load_col<MM>(cp + b * MM, cv);
+                    for (int q = 0; q < RB; ++q) w[q] = 0u;
 #pragma unroll
-                    for (int q = 0; q < RB; ++q) {
-                        bool p = true;
+                    for (int b = 0; b < 32; ++b) {
+                        float cv[C];
+                        load_col<C>(cp + b * C, cv);
 #pragma unroll
-                        for (int k = 0; k < MM; ++k) p = p && (xi[q][k] <= cv[k]);
-                        if (p) w[q] |= (1u << b);
+                        for (int q = 0; q < RB; ++q) {
+                            bool p = true;
+#pragma unroll
+                            for (int k = 0; k < C; ++k) p = p && (xi[q][k] <= cv[k]);
+                            if (p) w[q] |= (1u << b);
+                        }
+                    }
+#pragma unroll
+                    for (int q = 0; q < RB; ++q) {                      // unique rows: only i == j is "equal"
+                        const int d = rs + q * 32 + lane - cb;
+                        if (d >= 0 && d < 32) w[q] &= ~(1u << d);
+                    }
+                } else if constexpr (M == 1) {
+#pragma unroll
+                    for (int q = 0; q < RB; ++q) w[q] = 0xFFFFFFFFu;    // lower block: f0 <= by order
+                } else {
+                    const float cmin = cp[0], cmax = cp[(ncol - 1) * C];
+                    if (rmin > cmax) {                                  // every row's f1 > every column's
+#pragma unroll
+                        for (int q = 0; q < RB; ++q) w[q] = 0u;
+                    } else {
+                        if (rmax <= cmin) word_sign<C, 1>(cp, xi, w);   // f1 passes for every pair
+                        else word_sign<C, 0>(cp, xi, w);
+#pragma unroll
+                        for (int q = 0; q < RB; ++q) w[q] = ~w[q];      // fail bits -> pass bits
                     }
                 }
-                if (MM == 0) {                                          // M == 1: only the order matters
+                const uint32_t cmask = (ncol >= 32) ? 0xFFFFFFFFu : ((1u << ncol) - 1u);
 #pragma unroll
-                    for (int q = 0; q < RB; ++q) {
-                        const int i = rs + q * 32 + lane;
-                        uint32_t v = 0u;
-                        for (int b = 0; b < 32; ++b) v |= (uint32_t)(i < U && cb + b < U) << b;
-                        w[q] = v;
-                    }
-                }
-                if (cb <= rs + SLAB - 1) {                              // touches the diagonal: keep j > i only
-#pragma unroll
-                    for (int q = 0; q < RB; ++q) {
-                        const int i = rs + q * 32 + lane;
-                        const int sh = i - cb + 1;                      // bits below sh are j <= i
-                        w[q] = (sh <= 0) ? w[q] : (sh >= 32 ? 0u : (w[q] & (0xFFFFFFFFu << sh)));
-                    }
-                }
+                for (int q = 0; q < RB; ++q) w[q] = (rs + q * 32 + lane < U) ? (w[q] & cmask) : 0u;
             }
 #pragma unroll
             for (int q = 0; q < RB; ++q) st[wc * (SLAB + 1) + q * 32 + lane] = w[q];
@@ -302,9 +398,26 @@ k_dominance_tiles(const float* __restrict__ ucols, int64_t npad, const Scal* __r
     }
 }
 
-// Fallback for M-1 > MAX_TEMPLATE_MM: same tiling, objective loop at run time, one row per lane.
+template <int M>
 __global__ void __launch_bounds__(TILE_WARPS * 32)
-k_dominance_tiles_generic(const float* __restrict__ ucols, int64_t npad, int mm, const Scal* __restrict__ scal,
+k_dominance_tiles(const float* __restrict__ ucols, int64_t npad, const Scal* __restrict__ scal,
+                  uint32_t* __restrict__ bits, int* __restrict__ count, int world, int rank) {
+    const int l = blockIdx.y;
+    const int J = l * world + rank;
+    const int U = scal->U;
+    const int col0 = J * TW;
+    if (col0 >= U) return;
+    const int rowlimit = min((J + 1) * TW, U);
+    const int row0 = blockIdx.x * CTA_ROWS;
+    if (row0 >= rowlimit) return;
+    extern __shared__ __align__(16) uint32_t smem[];
+    if (row0 >= col0) tile_body<M, true>(ucols, npad, U, l, J, col0, row0, rowlimit, bits, count, world, rank, smem);
+    else tile_body<M, false>(ucols, npad, U, l, J, col0, row0, rowlimit, bits, count, world, rank, smem);
+}
+
+// Fallback for M > MAX_TEMPLATE_M: same labelling and layout, objective loop at run time.
+__global__ void __launch_bounds__(TILE_WARPS * 32)
+k_dominance_tiles_generic(const float* __restrict__ ucols, int64_t npad, int m, const Scal* __restrict__ scal,
                           uint32_t* __restrict__ bits, int* __restrict__ count, int world, int rank) {
     const int l = blockIdx.y;
     const int J = l * world + rank;
@@ -314,13 +427,8 @@ k_dominance_tiles_generic(const float* __restrict__ ucols, int64_t npad, int mm,
     const int rowlimit = min((J + 1) * TW, U);
     const int row0 = blockIdx.x * (TILE_WARPS * 32);
     if (row0 >= rowlimit) return;
-    extern __shared__ __align__(16) uint32_t smem[];
-    float* colv = reinterpret_cast<float*>(smem);                       // [TW][mm]
-    for (int t = threadIdx.x; t < mm * TW; t += blockDim.x) {
-        const int c = t / mm, k = t - c * mm;
-        colv[t] = ucols[(int64_t)k * npad + col0 + c];
-    }
-    __syncthreads();
+    const bool diag = row0 >= col0;
+    const int k0 = diag ? 0 : 1;
     const int i = row0 + threadIdx.x;
     uint32_t* gout = bits + d_panel_words_before(l, world, rank) + (int64_t)i * PW;
     for (int wc = 0; wc < PW; ++wc) {
@@ -328,8 +436,8 @@ k_dominance_tiles_generic(const float* __restrict__ ucols, int64_t npad, int mm,
         uint32_t w = 0u;
         for (int b = 0; b < 32; ++b) {
             const int j = cb + b;
-            bool p = (j > i);
-            for (int k = 0; k < mm && p; ++k) p = ucols[(int64_t)k * npad + i] <= colv[(wc * 32 + b) * mm + k];
+            bool p = (i < U) && (j < U) && (i != j);
+            for (int k = k0; k < m && p; ++k) p = ucols[(int64_t)k * npad + i] <= ucols[(int64_t)k * npad + j];
             w |= (uint32_t)p << b;
             if (p) atomicAdd(&count[(int64_t)l * TW + wc * 32 + b], 1);
         }
@@ -447,6 +555,247 @@ k_front_apply(const uint32_t* __restrict__ bits, int* __restrict__ count, const 
     }
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// stage 3b: the whole peel as ONE persistent cooperative kernel (single-rank path)
+// ------------------------------------------------------------------------------------------------
+// Each CTA owns a fixed set of panels (heaviest first, dealt boustrophedon so the triangular panel
+// sizes balance).  The dominator counts of a panel live BIT-SLICED (in shared memory when they fit,
+// else in global memory), owned by that CTA alone: plane p, word w holds bit p of the counts of
+// columns 32w..32w+31.  Per front and panel: the CTA's 16 warps stream the front's 128-byte row
+// segments (lane <-> word, 32 rows in flight per warp) into carry-save adders, the per-warp sums
+// are merged bit-sliced through shared memory, warp 0 subtracts the merged sum from the count
+// planes with a bit-sliced borrow chain, and "count == 0" is simply the NOR of the planes - which
+// IS the next front's membership mask for these 32 x 32 columns.  Nothing is ever expanded to
+// integers.  One grid-wide barrier per front.
+namespace cg = cooperative_groups;
+
+constexpr int PEEL_WARPS = 16;
+constexpr int PEEL_UP = 9;                          // register planes 8 .. 2^11 (+ ones, twos, fours)
+constexpr int PEEL_RP = 3 + PEEL_UP;                // 12 planes per warp: up to 4095 rows per pass
+constexpr int PEEL_PM = PEEL_RP + 4;                // merged over 16 warps: 16 planes (16*4095 < 2^16)
+constexpr int PEEL_ROWS_PER_WARP = (1 << PEEL_RP) - 32;
+constexpr int PEEL_ROWS_PER_PASS = PEEL_WARPS * PEEL_ROWS_PER_WARP;
+
+__device__ __forceinline__ uint32_t ld_stream(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+
+__device__ __forceinline__ int peel_owner_panel(int q, int npl) { return npl - 1 - q; }   // heaviest first
+
+struct PeelShared {
+    uint32_t merge[PEEL_WARPS][PEEL_PM][32];
+    uint32_t newmask[32];
+    int nf;
+};
+
+// Grid-wide barrier on a monotonically increasing counter (all CTAs are co-resident: cooperative
+// launch).  `epoch` counts the barriers this CTA has passed.  Only thread 0 touches global memory:
+// it also fetches the size of the front about to be processed, so 4 700 warps do not all hit the
+// same L2 word right after the barrier.
+__device__ __forceinline__ int grid_barrier(unsigned int* ctr, unsigned int& epoch, const int* nf_ptr, int* nf_smem) {
+    __syncthreads();
+    ++epoch;
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(ctr, 1u);
+        const unsigned int target = epoch * gridDim.x;
+        unsigned int v;
+        do {
+            asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+        } while (v < target);
+        __threadfence();
+        int nf;
+        asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(nf) : "l"(nf_ptr) : "memory");
+        *nf_smem = nf;
+    }
+    __syncthreads();
+    return *nf_smem;
+}
+
+// Warp 0: subtract `delta` (bit-sliced, `pm` planes in shared memory; null = zero) from a panel's
+// count planes, find the columns that reached zero, retire them, publish them as the next front.
+__device__ __forceinline__ void peel_commit(uint32_t* cp, int K, const uint32_t (*delta)[32], int pm, int lane,
+                                            int J, int* flist_next, int* nf_next, uint32_t* newmask_out) {
+    uint32_t borrow = 0, nz = 0;
+    for (int p = 0; p < K; ++p) {
+        const uint32_t c = cp[p * PW + lane];
+        const uint32_t d = (p < pm) ? delta[p][lane] : 0u;
+        const uint32_t x = c ^ d;
+        const uint32_t r = x ^ borrow;
+        borrow = (~c & d) | (~x & borrow);
+        if (pm > 0) cp[p * PW + lane] = r;
+        nz |= r;
+    }
+    uint32_t alive = cp[K * PW + lane];
+    const uint32_t nw = alive & ~nz;
+    alive &= ~nw;
+    cp[K * PW + lane] = alive;
+    newmask_out[lane] = nw;
+    // publish: exclusive prefix of popcounts across the warp, one atomic per warp
+    const int c = __popc(nw);
+    int incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    const int total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+    int base = 0;
+    if (lane == 0 && total) base = atomicAdd(nf_next, total);
+    base = __shfl_sync(0xFFFFFFFFu, base, 0) + incl - c;
+    uint32_t w = nw;
+    const int col0 = J * TW + lane * 32;
+    while (w) {
+        const int b = __ffs(w) - 1;
+        w &= w - 1;
+        flist_next[base++] = col0 + b;
+    }
+}
+
+__device__ __forceinline__ void csa8(uint32_t& ones, uint32_t& twos, uint32_t& fours, uint32_t (&up)[PEEL_UP],
+                                     const uint32_t* x) {
+    uint32_t ta, tb, fa, fb, e;
+    csa(ta, ones, ones, x[0], x[1]);
+    csa(tb, ones, ones, x[2], x[3]);
+    csa(fa, twos, twos, ta, tb);
+    csa(ta, ones, ones, x[4], x[5]);
+    csa(tb, ones, ones, x[6], x[7]);
+    csa(fb, twos, twos, ta, tb);
+    csa(e, fours, fours, fa, fb);
+#pragma unroll
+    for (int p = 0; p < PEEL_UP; ++p) {
+        if (!__any_sync(0xFFFFFFFFu, e)) break;
+        const uint32_t c = up[p] & e;
+        up[p] ^= e;
+        e = c;
+    }
+}
+
+__global__ void __launch_bounds__(PEEL_WARPS * 32, 2)
+k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ count, int* __restrict__ rank_u,
+                  int* flistA, int* flistB, Scal* scal, uint32_t* __restrict__ cplanes, int npl, int K, int world,
+                  int rank, int planes_in_smem) {
+    extern __shared__ __align__(16) unsigned char peel_smem_raw[];
+    PeelShared& sh = *reinterpret_cast<PeelShared*>(peel_smem_raw);
+    uint32_t* cp_smem = reinterpret_cast<uint32_t*>(peel_smem_raw + sizeof(PeelShared));
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int G = gridDim.x, B = blockIdx.x;
+    const int U = scal->U;
+    const size_t cp_stride = (size_t)(K + 1) * PW;
+    unsigned int epoch = 0;
+    unsigned int* bar = reinterpret_cast<unsigned int*>(&scal->barrier);
+
+    // ---- init: int counts -> planes, alive mask, front 0 -----------------------------------------
+    for (int q0 = 0, slot = 0; q0 < npl; q0 += G, ++slot) {
+        const int q = q0 + ((slot & 1) ? (G - 1 - B) : B);
+        if (q >= npl) continue;                                     // CTA-uniform
+        const int l = peel_owner_panel(q, npl);
+        const int J = l * world + rank;
+        uint32_t* cp = planes_in_smem ? cp_smem + slot * cp_stride : cplanes + (size_t)l * cp_stride;
+        for (int c = threadIdx.x; c < TW; c += blockDim.x) {        // 32 consecutive columns per warp step
+            const int j = J * TW + c;
+            const int v = (j < U) ? count[(size_t)l * TW + c] : 0;
+            for (int p = 0; p < K; ++p) {
+                const uint32_t w = __ballot_sync(0xFFFFFFFFu, (v >> p) & 1);
+                if (lane == 0) cp[p * PW + (c >> 5)] = w;
+            }
+            const uint32_t a = __ballot_sync(0xFFFFFFFFu, j < U);
+            if (lane == 0) cp[K * PW + (c >> 5)] = a;
+        }
+        __syncthreads();
+        if (warp == 0) peel_commit(cp, K, nullptr, 0, lane, J, flistA, &scal->nf3[0], sh.newmask);
+        __syncthreads();
+        for (int c = threadIdx.x; c < TW; c += blockDim.x)
+            if ((sh.newmask[c >> 5] >> (c & 31)) & 1u) rank_u[(size_t)l * TW + c] = 0;
+        __syncthreads();
+    }
+    int nf = grid_barrier(bar, epoch, &scal->nf3[0], &sh.nf);
+
+    // ---- fronts ----------------------------------------------------------------------------------
+    int k = 0;
+    for (;; ++k) {
+        if (nf == 0) break;
+        if (B == 0 && threadIdx.x == 0) scal->nf3[(k + 2) % 3] = 0;
+        const int* fl = (k & 1) ? flistB : flistA;
+        int* fl_next = (k & 1) ? flistA : flistB;
+        for (int q0 = 0, slot = 0; q0 < npl; q0 += G, ++slot) {
+            const int q = q0 + ((slot & 1) ? (G - 1 - B) : B);
+            if (q >= npl) continue;
+            const int l = peel_owner_panel(q, npl);
+            const int J = l * world + rank;
+            if (J * TW >= U) continue;
+            const int rowlimit = min((J + 1) * TW, U);
+            const uint32_t* pbase = bits + d_panel_words_before(l, world, rank) + lane;
+            uint32_t* cp = planes_in_smem ? cp_smem + slot * cp_stride : cplanes + (size_t)l * cp_stride;
+
+            for (int pass0 = 0; pass0 < nf; pass0 += PEEL_ROWS_PER_PASS) {
+                const int pass_n = min(nf - pass0, PEEL_ROWS_PER_PASS);
+                // groups of 32 consecutive list entries are dealt to the warps round-robin (the list
+                // is grouped by publishing panel, so contiguous slices would be badly unbalanced)
+                const int hi = pass0 + pass_n;
+                const int groups = (pass_n + 31) >> 5;
+                const int per = ((groups + PEEL_WARPS - 1) / PEEL_WARPS) << 5;   // rows a warp can see
+                int rp = 1;                                          // planes a warp can have touched
+                while ((1 << rp) <= per) ++rp;
+                rp = min(rp, PEEL_RP);
+                const int pm = min(rp + 4, PEEL_PM);
+                uint32_t ones = 0, twos = 0, fours = 0, up[PEEL_UP];
+#pragma unroll
+                for (int p = 0; p < PEEL_UP; ++p) up[p] = 0;
+                const int lo = pass0 + warp * 32, step = PEEL_WARPS * 32;
+                int mine = (lo + lane < hi) ? __ldcg(fl + lo + lane) : 0x7FFFFFFF;
+                for (int t0 = lo; t0 < hi; t0 += step) {
+                    const int nxt = (t0 + step + lane < hi) ? __ldcg(fl + t0 + step + lane) : 0x7FFFFFFF;
+                    uint32_t v[32];
+#pragma unroll
+                    for (int u = 0; u < 32; ++u) {
+                        const int i = __shfl_sync(0xFFFFFFFFu, mine, u);
+                        v[u] = (i < rowlimit) ? ld_stream(pbase + (size_t)i * PW) : 0u;
+                    }
+                    csa8(ones, twos, fours, up, v);
+                    csa8(ones, twos, fours, up, v + 8);
+                    csa8(ones, twos, fours, up, v + 16);
+                    csa8(ones, twos, fours, up, v + 24);
+                    mine = nxt;
+                }
+                // per-warp planes -> shared memory (only the planes that can be non-zero)
+                sh.merge[warp][0][lane] = ones;
+                sh.merge[warp][1][lane] = twos;
+                sh.merge[warp][2][lane] = fours;
+#pragma unroll
+                for (int p = 0; p < PEEL_UP; ++p)
+                    if (3 + p < pm) sh.merge[warp][3 + p][lane] = up[p];
+                for (int p = PEEL_RP; p < pm; ++p) sh.merge[warp][p][lane] = 0u;
+                __syncthreads();
+                // bit-sliced tree merge: warp w += warp w + half
+                for (int half = PEEL_WARPS / 2; half >= 1; half >>= 1) {
+                    if (warp < half) {
+                        uint32_t carry = 0;
+                        for (int p = 0; p < pm; ++p) {
+                            const uint32_t a = sh.merge[warp][p][lane], b = sh.merge[warp + half][p][lane];
+                            const uint32_t x = a ^ b;
+                            sh.merge[warp][p][lane] = x ^ carry;
+                            carry = (a & b) | (x & carry);
+                        }
+                    }
+                    __syncthreads();
+                }
+                if (warp == 0)
+                    peel_commit(cp, K, sh.merge[0], pm, lane, J, fl_next, &scal->nf3[(k + 1) % 3], sh.newmask);
+                __syncthreads();
+                for (int c = threadIdx.x; c < TW; c += blockDim.x)
+                    if ((sh.newmask[c >> 5] >> (c & 31)) & 1u) rank_u[(size_t)l * TW + c] = k + 1;
+                __syncthreads();
+            }
+        }
+        nf = grid_barrier(bar, epoch, &scal->nf3[(k + 1) % 3], &sh.nf);
+    }
+    if (B == 0 && threadIdx.x == 0) scal->fronts = k;
+}
+
 __global__ void k_write_ranks(const int* __restrict__ row2u, const int* __restrict__ rank_u, int64_t n, int world,
                               int rank, int* __restrict__ out) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -469,13 +818,13 @@ struct Plan {
     template <class T> T* at(size_t off) const { return reinterpret_cast<T*>(ws + off); }
 };
 
-template <int MM>
+template <int M>
 static int launch_tiles(const Plan& P, cudaStream_t s) {
     const Layout& L = P.L;
-    const size_t smem = sizeof(uint32_t) * ((size_t)MM * TW + (size_t)TILE_WARPS * PW * (SLAB + 1) + TW);
-    EVX_CUDA(cudaFuncSetAttribute(k_dominance_tiles<MM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const size_t smem = sizeof(uint32_t) * ((size_t)M * TW + (size_t)TILE_WARPS * PW * (SLAB + 1) + TW);
+    EVX_CUDA(cudaFuncSetAttribute(k_dominance_tiles<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((unsigned)ceil_div(L.npad, CTA_ROWS), (unsigned)L.npl);
-    k_dominance_tiles<MM><<<grid, TILE_WARPS * 32, smem, s>>>(P.at<float>(L.ucols), L.npad, P.at<Scal>(L.scal),
+    k_dominance_tiles<M><<<grid, TILE_WARPS * 32, smem, s>>>(P.at<float>(L.ucols), L.npad, P.at<Scal>(L.scal),
                                                               P.at<uint32_t>(L.bits), P.at<int>(L.count), L.world,
                                                               L.rank);
     EVX_LAUNCH_CHECK();
@@ -491,7 +840,7 @@ static int build(const Plan& P, const float* x, cudaStream_t s, cudaEvent_t tile
     const unsigned gn = (unsigned)ceil_div(n, T);
     Scal* scal = P.at<Scal>(L.scal);
     EVX_CUDA(cudaMemsetAsync(scal, 0, sizeof(Scal), s));
-    EVX_CUDA(cudaMemsetAsync(P.at<char>(L.ucols), 0xFF, sizeof(float) * (size_t)(m > 1 ? m - 1 : 1) * L.npad, s));
+    EVX_CUDA(cudaMemsetAsync(P.at<char>(L.ucols), 0xFF, sizeof(float) * (size_t)m * L.npad, s));
     EVX_CUDA(cudaMemsetAsync(P.at<char>(L.count), 0, sizeof(int) * (size_t)L.npl_max * TW, s));
     EVX_CUDA(cudaMemsetAsync(P.at<char>(L.rank_u), 0, sizeof(int) * (size_t)L.npl_max * TW, s));
 
@@ -513,15 +862,28 @@ static int build(const Plan& P, const float* x, cudaStream_t s, cudaEvent_t tile
     size_t tb = L.cubtmp_bytes;
     EVX_CUDA(cub::DeviceScan::InclusiveSum(P.at<void>(L.cubtmp), tb, P.at<int>(L.flags), P.at<int>(L.incl), (int)n, s));
     k_scatter_unique<<<gn, T, 0, s>>>(x, idx_cur, P.at<int>(L.incl), P.at<int>(L.flags), n, m, L.npad, scal,
-                                      P.at<float>(L.ucols), P.at<int>(L.row2u));
+                                      P.at<float>(L.tcols), P.at<int>(L.row2u));
     EVX_LAUNCH_CHECK();
+    // block-local f1 order (stable 64-bit radix sort on (block, f1 key)), then gather into place
+    {
+        int bbits = 1;
+        while ((1ll << bbits) < L.np + 1) ++bbits;
+        k_block_keys<<<gn, T, 0, s>>>(P.at<float>(L.tcols), n, L.npad, m, L.np, scal, P.at<uint64_t>(L.bkeyA), idx_cur);
+        EVX_LAUNCH_CHECK();
+        size_t tb2 = L.cubtmp_bytes;
+        EVX_CUDA(cub::DeviceRadixSort::SortPairs(P.at<void>(L.cubtmp), tb2, P.at<uint64_t>(L.bkeyA),
+                                                 P.at<uint64_t>(L.bkeyB), idx_cur, idx_nxt, (int)n, 0, 32 + bbits, s));
+        k_block_permute<<<gn, T, 0, s>>>(P.at<float>(L.tcols), idx_nxt, n, L.npad, m, scal, P.at<float>(L.ucols),
+                                         P.at<int>(L.label));
+        EVX_LAUNCH_CHECK();
+        k_relabel_rows<<<gn, T, 0, s>>>(P.at<int>(L.row2u), P.at<int>(L.label), n);
+        EVX_LAUNCH_CHECK();
+    }
 
     if (L.npl == 0) return EVX_OK;
-    const int mm = m - 1;
     int rc = EVX_OK;
     if (tiles_begin) EVX_CUDA(cudaEventRecord(tiles_begin, s));
-    switch (mm) {
-        case 0: rc = launch_tiles<0>(P, s); break;
+    switch (m) {
         case 1: rc = launch_tiles<1>(P, s); break;
         case 2: rc = launch_tiles<2>(P, s); break;
         case 3: rc = launch_tiles<3>(P, s); break;
@@ -533,13 +895,11 @@ static int build(const Plan& P, const float* x, cudaStream_t s, cudaEvent_t tile
         case 9: rc = launch_tiles<9>(P, s); break;
         case 10: rc = launch_tiles<10>(P, s); break;
         case 11: rc = launch_tiles<11>(P, s); break;
+        case 12: rc = launch_tiles<12>(P, s); break;
         default: {
-            const size_t smem = sizeof(float) * (size_t)mm * TW;
-            EVX_CUDA(cudaFuncSetAttribute(k_dominance_tiles_generic, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          (int)smem));
             dim3 grid((unsigned)ceil_div(L.npad, TILE_WARPS * 32), (unsigned)L.npl);
-            k_dominance_tiles_generic<<<grid, TILE_WARPS * 32, smem, s>>>(
-                P.at<float>(L.ucols), L.npad, mm, scal, P.at<uint32_t>(L.bits), P.at<int>(L.count), L.world, L.rank);
+            k_dominance_tiles_generic<<<grid, TILE_WARPS * 32, 0, s>>>(
+                P.at<float>(L.ucols), L.npad, m, scal, P.at<uint32_t>(L.bits), P.at<int>(L.count), L.world, L.rank);
             EVX_LAUNCH_CHECK();
         }
     }
@@ -572,6 +932,48 @@ static int apply(const Plan& P, int k, const uint32_t* masks, int* any_out, cuda
                                                     P.at<Scal>(L.scal), k, L.world, L.rank, any_out);
     EVX_LAUNCH_CHECK();
     return EVX_OK;
+}
+
+
+// Launch the persistent peel (single rank).  Returns EVX_OK and leaves the front count in scal->fronts.
+static int peel_persistent(const Plan& P, cudaStream_t s) {
+    const Layout& L = P.L;
+    int dev = 0, sms = 0, per_sm = 0;
+    EVX_CUDA(cudaGetDevice(&dev));
+    EVX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    // Count planes go to shared memory when every CTA's share fits beside the merge buffer with two
+    // CTAs per SM; otherwise they stay in the workspace (L2-resident, touched only by their owner).
+    const size_t base_smem = sizeof(PeelShared);
+    const size_t cp_bytes = sizeof(uint32_t) * (size_t)(L.kplanes + 1) * PW;
+    int target = sms * 2;
+    if (target > L.npl) target = L.npl;
+    if (target < 1) target = 1;
+    const size_t slots = (size_t)ceil_div(L.npl, target);
+    int planes_in_smem = (base_smem + slots * cp_bytes <= 100 * 1024) ? 1 : 0;
+    const size_t smem = base_smem + (planes_in_smem ? slots * cp_bytes : 0);
+    EVX_CUDA(cudaFuncSetAttribute(k_peel_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    EVX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_peel_persistent, PEEL_WARPS * 32, smem));
+    EVX_REQUIRE(per_sm >= 1, EVX_ERR_CUDA, "persistent peel kernel does not fit on an SM");
+    int grid = sms * per_sm;
+    if (grid > target) grid = target;
+    if (planes_in_smem && (size_t)ceil_div(L.npl, grid) > slots) planes_in_smem = 0;   // fewer CTAs than planned
+    const uint32_t* bits = P.at<uint32_t>(L.bits);
+    const int* count = P.at<int>(L.count);
+    int* rank_u = P.at<int>(L.rank_u);
+    int* fa = P.at<int>(L.flist);
+    int* fb = P.at<int>(L.flist2);
+    Scal* scal = P.at<Scal>(L.scal);
+    uint32_t* cpl = P.at<uint32_t>(L.cplanes);
+    int npl = L.npl, K = L.kplanes, world = L.world, rank = L.rank;
+    void* args[] = {&bits, &count, &rank_u, &fa, &fb, &scal, &cpl, &npl, &K, &world, &rank, &planes_in_smem};
+    EVX_CUDA(cudaLaunchCooperativeKernel((void*)k_peel_persistent, dim3(grid), dim3(PEEL_WARPS * 32), args, smem, s));
+    ++evx::launch_counter();
+    return EVX_OK;
+}
+
+static bool use_stepwise_peel() {
+    const char* e = getenv("EVX_PEEL");
+    return e && strcmp(e, "stepwise") == 0;
 }
 
 static thread_local int32_t g_last_fronts = 0;
@@ -676,7 +1078,12 @@ extern "C" int evx_nds_f32(const float* x, int64_t n, int32_t m, int32_t* rank, 
     uint32_t* mask = P.at<uint32_t>(P.L.mask);
     int host_any[ANY_SLOTS];
     int k = 0, batch = 8;
-    for (;;) {
+    const bool stepwise = use_stepwise_peel();
+    if (!stepwise) {
+        // default: one persistent cooperative kernel peels every front without host round trips
+        if ((rc = peel_persistent(P, s))) return rc;
+    }
+    for (; stepwise;) {
         for (int b = 0; b < batch; ++b) {
             if ((rc = detect(P, k + b, mask, s))) return rc;
             if ((rc = apply(P, k + b, mask, &scal->any[b], s))) return rc;
@@ -692,7 +1099,10 @@ extern "C" int evx_nds_f32(const float* x, int64_t n, int32_t m, int32_t* rank, 
     k_write_ranks<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(P.at<int>(P.L.row2u), P.at<int>(P.L.rank_u), n, 1, 0, rank);
     EVX_LAUNCH_CHECK();
     if (pf.on) EVX_CUDA(cudaEventRecord(pf.ev[3], s));
+    int fronts_dev = 0;
+    if (!stepwise) EVX_CUDA(cudaMemcpyAsync(&fronts_dev, &scal->fronts, sizeof(int), cudaMemcpyDeviceToHost, s));
     EVX_CUDA(cudaStreamSynchronize(s));
+    if (!stepwise) g_last_fronts = fronts_dev;
     if (pf.on) {
         EVX_CUDA(cudaEventElapsedTime(&pf.prep_ms, pf.ev[0], pf.ev[1]));
         EVX_CUDA(cudaEventElapsedTime(&pf.tiles_ms, pf.ev[1], pf.ev[2]));
