@@ -31,10 +31,10 @@ namespace evx {
 
 constexpr int TW = 1024;            // columns per panel
 constexpr int PW = TW / 32;         // words per panel row (128 B)
-constexpr int RB = 4;               // rows per lane in the tile kernel
+constexpr int RB = 2;               // rows per lane in the tile kernel
 constexpr int TILE_WARPS = 4;
-constexpr int SLAB = 32 * RB;       // rows per warp
-constexpr int CTA_ROWS = SLAB * TILE_WARPS;
+constexpr int SLAB = 32 * RB;       // rows per warp and pass
+constexpr int MAX_SLABS = 4;        // passes per warp (count planes stay in registers across passes)
 constexpr int APPLY_WARPS = 8;
 constexpr int ANY_SLOTS = 64;
 
@@ -246,34 +246,52 @@ __device__ __forceinline__ void word_sign(const float* cp, const float (&xi)[RB]
 #pragma unroll
     for (int q = 0; q < RB; ++q) w[q] = 0u;
     if constexpr (K0 >= C) return;                    // nothing left to test: every pair passes
+    if constexpr (C == 2) {                           // M = 3: two columns per 16-byte broadcast load
 #pragma unroll
-    for (int b = 31; b >= 0; --b) {
-        float cv[C];
-        load_col<C>(cp + b * C, cv);
+        for (int b = 30; b >= 0; b -= 2) {
+            const float4 v = *reinterpret_cast<const float4*>(cp + b * 2);   // col b: (x,y), col b+1: (z,w)
 #pragma unroll
-        for (int q = 0; q < RB; ++q) {
-            uint32_t f = 0u;
+            for (int q = 0; q < RB; ++q) {
+                uint32_t f1 = __float_as_uint(v.w - xi[q][1]), f0 = __float_as_uint(v.y - xi[q][1]);
+                if constexpr (K0 == 0) {
+                    f1 |= __float_as_uint(v.z - xi[q][0]);
+                    f0 |= __float_as_uint(v.x - xi[q][0]);
+                }
+                w[q] = __funnelshift_l(f1, w[q], 1);
+                w[q] = __funnelshift_l(f0, w[q], 1);
+            }
+        }
+    } else {
 #pragma unroll
-            for (int k = K0; k < C; ++k) f |= __float_as_uint(cv[k] - xi[q][k]);
-            w[q] = __funnelshift_l(f, w[q], 1);       // (w << 1) | sign(f)
+        for (int b = 31; b >= 0; --b) {
+            float cv[C];
+            load_col<C>(cp + b * C, cv);
+#pragma unroll
+            for (int q = 0; q < RB; ++q) {
+                uint32_t f = 0u;
+#pragma unroll
+                for (int k = K0; k < C; ++k) f |= __float_as_uint(cv[k] - xi[q][k]);
+                w[q] = __funnelshift_l(f, w[q], 1);   // (w << 1) | sign(f)
+            }
         }
     }
 }
 
-// One CTA: CTA_ROWS dominator rows x one panel (TW columns).  Lane <-> row (RB rows per lane, values
-// in registers); the panel's column values sit in shared memory and are broadcast one column per
-// step; each lane assembles its own 32-bit words.  Words are staged through shared memory so the
-// 128-byte panel rows leave as full coalesced lines, and the same pass over the staged words feeds
-// carry-save adders that produce the column counts.
-// M = objectives.  Off-diagonal CTAs stage objectives 1..M-1 (C = M-1 values per point), the
-// diagonal CTAs of a panel stage all M.
+// One CTA: TILE_WARPS x `slabs` slabs of SLAB dominator rows against one panel (TW columns).
+// Lane <-> row (RB rows per lane, values in registers); the panel's column values sit in shared
+// memory and are broadcast; each lane assembles its own 32-bit words.  Words are staged through
+// shared memory so the 128-byte panel rows leave as full coalesced lines, and the same pass over
+// the staged words feeds carry-save adders whose planes persist over the warp's slabs and become
+// the column counts.  M = objectives.  Off-diagonal CTAs stage objectives 1..M-1 (C = M-1 values
+// per point); the diagonal CTAs of a panel stage all M.
 template <int M, bool DIAG>
 __device__ __forceinline__ void tile_body(const float* __restrict__ ucols, int64_t npad, int U, int l, int J,
-                                          int col0, int row0, int rowlimit, uint32_t* __restrict__ bits,
+                                          int col0, int row0, int rowlimit, int slabs, uint32_t* __restrict__ bits,
                                           int* __restrict__ count, int world, int rank, uint32_t* smem) {
     constexpr int C = DIAG ? M : (M > 1 ? M - 1 : 1);      // staged values per point
     constexpr int KOFF = DIAG ? 0 : 1;                     // first staged objective
     constexpr bool HAVE = DIAG || M > 1;                   // any objective staged at all
+    constexpr int NUP = 6;                                 // planes 8 .. 256 (MAX_SLABS * SLAB rows)
     float* colv = reinterpret_cast<float*>(smem);                          // [TW][C]
     uint32_t* stage = smem + M * TW;                                       // [TILE_WARPS][PW][SLAB+1]
     int* scount = reinterpret_cast<int*>(stage + TILE_WARPS * PW * (SLAB + 1));   // [TW]
@@ -288,8 +306,17 @@ __device__ __forceinline__ void tile_body(const float* __restrict__ ucols, int64
     __syncthreads();
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int rs = row0 + warp * SLAB;                                  // first row of this warp's slab
-    if (rs < rowlimit) {
+    uint32_t* st = stage + warp * PW * (SLAB + 1);
+    const uint32_t* sl = st + lane * (SLAB + 1);
+    uint32_t ones = 0, twos = 0, fours = 0, up[NUP];
+#pragma unroll
+    for (int p = 0; p < NUP; ++p) up[p] = 0;
+    bool any_rows = false;
+
+    for (int sidx = 0; sidx < slabs; ++sidx) {
+        const int rs = row0 + (sidx * TILE_WARPS + warp) * SLAB;            // first row of this slab
+        if (rs >= rowlimit) break;                                          // warp-uniform
+        any_rows = true;
         float xi[RB][C];
 #pragma unroll
         for (int q = 0; q < RB; ++q)
@@ -307,7 +334,6 @@ __device__ __forceinline__ void tile_body(const float* __restrict__ ucols, int64
             rmax = __shfl_sync(0xFFFFFFFFu, cand, last & 31);
         }
 
-        uint32_t* st = stage + warp * PW * (SLAB + 1);
         for (int wc = 0; wc < PW; ++wc) {
             const int cb = col0 + wc * 32;                              // first column of this word
             uint32_t w[RB];
@@ -363,8 +389,6 @@ __device__ __forceinline__ void tile_body(const float* __restrict__ ucols, int64
 
         // copy-out (lane <-> word column) fused with the vertical popcount of the slab
         uint32_t* gout = bits + d_panel_words_before(l, world, rank) + (int64_t)rs * PW;
-        uint32_t ones = 0, twos = 0, fours = 0, up[5] = {0, 0, 0, 0, 0};   // planes 8,16,32,64,128
-        const uint32_t* sl = st + lane * (SLAB + 1);
         for (int rl = 0; rl < SLAB; rl += 8) {
             uint32_t v[8];
 #pragma unroll
@@ -380,14 +404,17 @@ __device__ __forceinline__ void tile_body(const float* __restrict__ ucols, int64
             csa(fb, twos, twos, ta, tb);
             csa(e, fours, fours, fa, fb);
 #pragma unroll
-            for (int p = 0; p < 5; ++p) { const uint32_t c = up[p] & e; up[p] ^= e; e = c; }
+            for (int p = 0; p < NUP; ++p) { const uint32_t c = up[p] & e; up[p] ^= e; e = c; }
         }
+        __syncwarp();
+    }
+    if (any_rows) {
 #pragma unroll 4
         for (int bb = 0; bb < 32; ++bb) {
             const int bit = (bb + lane) & 31;
             int v = ((ones >> bit) & 1) | (((twos >> bit) & 1) << 1) | (((fours >> bit) & 1) << 2);
 #pragma unroll
-            for (int p = 0; p < 5; ++p) v |= ((up[p] >> bit) & 1) << (3 + p);
+            for (int p = 0; p < NUP; ++p) v |= ((up[p] >> bit) & 1) << (3 + p);
             if (v) atomicAdd(&scount[lane * 32 + bit], v);
         }
     }
@@ -401,18 +428,20 @@ __device__ __forceinline__ void tile_body(const float* __restrict__ ucols, int64
 template <int M>
 __global__ void __launch_bounds__(TILE_WARPS * 32)
 k_dominance_tiles(const float* __restrict__ ucols, int64_t npad, const Scal* __restrict__ scal,
-                  uint32_t* __restrict__ bits, int* __restrict__ count, int world, int rank) {
+                  uint32_t* __restrict__ bits, int* __restrict__ count, int world, int rank, int slabs) {
     const int l = blockIdx.y;
     const int J = l * world + rank;
     const int U = scal->U;
     const int col0 = J * TW;
     if (col0 >= U) return;
     const int rowlimit = min((J + 1) * TW, U);
-    const int row0 = blockIdx.x * CTA_ROWS;
+    const int row0 = blockIdx.x * (slabs * TILE_WARPS * SLAB);
     if (row0 >= rowlimit) return;
     extern __shared__ __align__(16) uint32_t smem[];
-    if (row0 >= col0) tile_body<M, true>(ucols, npad, U, l, J, col0, row0, rowlimit, bits, count, world, rank, smem);
-    else tile_body<M, false>(ucols, npad, U, l, J, col0, row0, rowlimit, bits, count, world, rank, smem);
+    if (row0 >= col0)
+        tile_body<M, true>(ucols, npad, U, l, J, col0, row0, rowlimit, slabs, bits, count, world, rank, smem);
+    else
+        tile_body<M, false>(ucols, npad, U, l, J, col0, row0, rowlimit, slabs, bits, count, world, rank, smem);
 }
 
 // Fallback for M > MAX_TEMPLATE_M: same labelling and layout, objective loop at run time.
@@ -823,10 +852,14 @@ static int launch_tiles(const Plan& P, cudaStream_t s) {
     const Layout& L = P.L;
     const size_t smem = sizeof(uint32_t) * ((size_t)M * TW + (size_t)TILE_WARPS * PW * (SLAB + 1) + TW);
     EVX_CUDA(cudaFuncSetAttribute(k_dominance_tiles<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    dim3 grid((unsigned)ceil_div(L.npad, CTA_ROWS), (unsigned)L.npl);
+    // rows per CTA = slabs * TILE_WARPS * SLAB (256 .. 1024, always dividing TW): as many passes per
+    // warp as still leave a few waves of CTAs on the chip
+    int slabs = MAX_SLABS;
+    while (slabs > 1 && (int64_t)L.npl * L.np * (TW / (slabs * TILE_WARPS * SLAB)) / 2 < 148 * 5 * 4) slabs >>= 1;
+    dim3 grid((unsigned)ceil_div(L.npad, slabs * TILE_WARPS * SLAB), (unsigned)L.npl);
     k_dominance_tiles<M><<<grid, TILE_WARPS * 32, smem, s>>>(P.at<float>(L.ucols), L.npad, P.at<Scal>(L.scal),
                                                               P.at<uint32_t>(L.bits), P.at<int>(L.count), L.world,
-                                                              L.rank);
+                                                              L.rank, slabs);
     EVX_LAUNCH_CHECK();
     return EVX_OK;
 }
