@@ -19,6 +19,7 @@ _SIGNATURES = {
     "evx_nds_f32": (ctypes.c_int, [c_vp, c_i64, c_i32, c_vp, c_vp, c_sz, c_vp]),
     "evx_nds_host_f32": (ctypes.c_int, [c_vp, c_i64, c_i32, c_vp]),
     "evx_nds_last_num_fronts": (c_i32, []),
+    "evx_nds_noalloc_f32": (ctypes.c_int, [c_vp, c_i64, c_i32, c_vp, c_vp]),
     "evx_rank_from_matrix_workspace_bytes": (c_sz, [c_i64]),
     "evx_rank_from_matrix_u8": (ctypes.c_int, [c_vp, c_vp, c_i64, c_vp, c_vp, c_sz, c_vp]),
     "evx_crowding_workspace_bytes": (c_sz, [c_i64, c_i32]),

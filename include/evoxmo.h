@@ -60,6 +60,24 @@ int evx_nds_host_f32(const float* x_host, int64_t n, int32_t m, int32_t* rank_ho
 /* Number of fronts found by the last evx_nds_* call on this host thread.                          */
 int32_t evx_nds_last_num_fronts(void);
 
+/* ---- non-dominated sort without any device allocation -------------------------------------------
+ * No counterpart in the reference (its non_dominated_sort always gets fresh arrays from XLA).
+ * For callers that cannot obtain device scratch memory at the point of the call: a custom-call
+ * handler that is handed only its input and output buffers, a callback that runs while the host
+ * framework's allocator is locked, a process whose free device memory all belongs to another pool.
+ * The scratch (n x n dominance bits + counts, about 2.1 MB) is a fixed array inside the library
+ * image, present on every GPU that loads the library until the process exits; hence the limit
+ * n <= EVX_NDS_NOALLOC_MAX_N, beyond which the call fails with EVX_ERR_ARG and a message.
+ * The call allocates nothing (no cudaMalloc / cudaFree / library temp storage), is asynchronous on
+ * `stream`, and gives the same ranks as evx_nds_f32.  x: device float32 [n, m]; rank: device int32 [n].
+ * - The first call on each device resolves the array's device address (cudaGetSymbolAddress, with
+ *   that device current); make that first call before starting any stream capture.
+ * - All calls on a device share the one array, which keeps the previous call's contents; what has to
+ *   start from zero is cleared by the call itself.  Two calls that overlap on the same GPU (different
+ *   streams or threads) race on it: serialise them.                                                 */
+#define EVX_NDS_NOALLOC_MAX_N 4096
+int evx_nds_noalloc_f32(const float* x, int64_t n, int32_t m, int32_t* rank, void* stream);
+
 /* ---- (a3) rank from a dense domination matrix ------------------------------------------------
  * replaces operators/selection/non_dominate.py:13-29  `host_rank_from_domination_matrix`
  * (the `method="host"` pure_callback, :65-72), on the device.
