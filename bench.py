@@ -35,6 +35,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-sample", type=int, default=0, help="rows of the CPU-baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-nsga2", action="store_true", help="skip the NSGA-II generations/s side measurement")
     return ap.parse_args()
 
 
@@ -283,6 +284,8 @@ def run_ours(args):
                                         "algorithmic_pairs_per_s": pairs / t}
         except Exception as e:                        # probe only supports m in {3, 10}
             line["compare_roofline"] = {"error": str(e)}
+    if world == 1 and not args.no_nsga2:
+        line["nsga2"] = nsga2_gens_per_s(torch)
     if not args.no_cpu_baseline:
         ns = auto_cpu_sample(m, args.seed, user=args.cpu_sample)
         rate, dt, cores = cpu_oracle_rate(ns, m, args.seed)
@@ -292,6 +295,29 @@ def run_ours(args):
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def nsga2_gens_per_s(torch, pop=100_000, d=12, m=3, gens=10):
+    """Second half of BASELINE.json's metric: NSGA-II generations/s at pop 100k on DTLZ2 (configs[2]):
+    variation kernel -> DTLZ2 evaluate -> concat -> non_dominate(2*pop -> pop), all on the device."""
+    import evox_b200 as E
+    from evox_b200.algorithms import NSGA2, run_generations
+    alg = NSGA2(torch.zeros(d), torch.ones(d), n_objs=m, pop_size=pop)
+    prob = E.problems.numerical.DTLZ2(d=d, m=m)
+    state = alg.setup(seed=0)
+    state, _ = run_generations(alg, prob, state, 3)                    # warm-up (first fronts are the deepest)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    state, _ = run_generations(alg, prob, state, gens)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    return {"metric": "nsga2_generations_per_s", "value": gens / (ms * 1e-3), "unit": "generations/s",
+            "ms_per_generation": ms / gens, "config": {"workload": f"NSGA-II DTLZ2 d={d} M={m} pop={pop} (merged N={2 * pop})",
+                                                       "generations_timed": gens, "after_warmup_generations": 3},
+            "note": "variation = evx_variation_sbx_pm_f32 (Philox; statistical parity with jax.random), "
+                    "selection glue = torch sorts as in non_dominate.py:210-222"}
 
 
 def main():

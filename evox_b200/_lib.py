@@ -29,6 +29,9 @@ _SIGNATURES = {
     "evx_eval_maf1_f32": (ctypes.c_int, [c_vp, c_i64, c_i32, c_i32, c_vp, c_vp]),
     "evx_lsmop_groups": (ctypes.c_int, [c_i32, c_i32, c_vp, c_vp]),
     "evx_eval_lsmop_f32": (ctypes.c_int, [c_i32, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp]),
+    "evx_variation_sbx_pm_f32": (ctypes.c_int, [c_vp, c_i64, c_i32, c_vp, c_vp, ctypes.c_float, ctypes.c_float,
+                                                ctypes.c_float, ctypes.c_float, ctypes.c_uint32, ctypes.c_uint32,
+                                                c_vp, c_vp]),
     "evx_nds_shard_workspace_bytes": (c_sz, [c_i64, c_i32, c_i32, c_i32]),
     "evx_nds_shard_create": (c_vp, [c_i64, c_i32, c_i32, c_i32, c_vp, c_sz]),
     "evx_nds_shard_destroy": (None, [c_vp]),

@@ -1,0 +1,1 @@
+from .nsga2 import NSGA2, run_generations  # noqa: F401

@@ -117,6 +117,16 @@ int evx_lsmop_groups(int32_t d, int32_t m, int32_t* sublen_host, int32_t* off_ho
 int evx_eval_lsmop_f32(int32_t which, const float* X, int64_t n, int32_t d, int32_t m,
                        const int32_t* sublen_host, const int32_t* off_host, float* F, void* stream);
 
+/* ---- (f2) NSGA-II variation -------------------------------------------------------------------
+ * replaces operators/crossover/sbx.py:8-40 (type 1), operators/mutation/pm_mutation.py:7-54 and the
+ * clip of algorithms/mo/nsga2.py:85 in one kernel.  pop, out: device float32 [n, d] (rows p and
+ * p + n/2 are mated; an odd last row passes through); lb, ub: device float32 [d].  Random numbers
+ * come from Philox4x32-10 keyed by (seed, generation): reproducible, statistically - not bitwise -
+ * equivalent to the reference's jax.random draws.  Asynchronous.                                   */
+int evx_variation_sbx_pm_f32(const float* pop, int64_t n, int32_t d, const float* lb, const float* ub,
+                             float pro_c, float dis_c, float pro_m, float dis_m, uint32_t seed,
+                             uint32_t generation, float* out, void* stream);
+
 /* ---- sharded non-dominated sort (one process per GPU; column panels dealt round-robin) --------
  * The exchange step between ranks - all-gather of each front's membership - is done by the caller
  * (torch.distributed / NCCL) between these calls; see INTEGRATION.md.  No reference counterpart:
