@@ -188,6 +188,18 @@ __global__ void k_block_keys(const float* __restrict__ tcols, int64_t n, int64_t
     vals[u] = (int)u;
 }
 
+// Second level: inside a block, every run of 32 consecutive (f1-ordered) positions - one bit-matrix
+// word - is re-ordered by f2, so that "f2_row <= f2_col" over a word is a suffix mask found by a
+// 5-step binary search instead of 32 compares.
+__global__ void k_word_keys(const float* __restrict__ tcols, const int* __restrict__ perm1, int64_t n, int64_t npad,
+                            int np, const Scal* __restrict__ scal, uint64_t* __restrict__ keys) {
+    const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= n) return;
+    const bool valid = v < scal->U;
+    keys[v] = valid ? (((uint64_t)(v >> 5) << 32) | float_key(tcols[2 * npad + perm1[v]]))
+                    : ((uint64_t)np * (TW / 32) << 32);
+}
+
 __global__ void k_block_permute(const float* __restrict__ tcols, const int* __restrict__ perm, int64_t n,
                                 int64_t npad, int m, const Scal* __restrict__ scal, float* __restrict__ ucols,
                                 int* __restrict__ label_of_u) {
@@ -234,187 +246,109 @@ __device__ __forceinline__ void load_col(const float* p, float (&v)[C]) {
     }
 }
 
-// 32 columns x RB rows per lane; objectives [K0, C) of the staged values take part.
 // The compare runs on the FMA pipe: for finite or infinite a, b (no NaN reaches here)
 //     a <= b   <=>   sign(b - a) == 0
 // (b - a is exactly signed: it rounds to zero only when a == b, and inf - inf gives the canonical
 // positive NaN, i.e. "pass", which is what inf <= inf says).  The fail bits of the objectives are
-// OR-ed (LOP3) and shifted into the word with one funnel shift (SHF): 2 FADD on the FMA pipe and
-// 2 ALU-pipe instructions per 32 pair tests at M = 3, instead of 3 ALU-pipe FSETP/SEL.
-template <int C, int K0>
-__device__ __forceinline__ void word_sign(const float* cp, const float (&xi)[RB][C], uint32_t (&w)[RB]) {
+// OR-ed (LOP3) and shifted into the word with one funnel shift (SHF), instead of FSETP chains on the
+// half-rate ALU pipe.
+//
+// Fail bits of 32 columns x RB rows for objective f1 (if F1) and the CR objectives 3 .. M-1.
+// f1w: the word's 32 f1 values (SoA); restw: its [32][CR] remaining values.
+template <int CR, bool F1>
+__device__ __forceinline__ void word_fail(const float* f1w, const float* restw, const float (&xf1)[RB],
+                                          const float (&xr)[RB][CR > 0 ? CR : 1], uint32_t (&w)[RB]) {
 #pragma unroll
     for (int q = 0; q < RB; ++q) w[q] = 0u;
-    if constexpr (K0 >= C) return;                    // nothing left to test: every pair passes
-    if constexpr (C == 2) {                           // M = 3: two columns per 16-byte broadcast load
+    if constexpr (!F1 && CR == 0) return;
+    if constexpr (CR == 0) {                          // f1 only: four columns per 16-byte broadcast load
+        // four independent shift chains per row (8 columns each) instead of one of 32
+        uint32_t a[RB][4];
 #pragma unroll
-        for (int b = 30; b >= 0; b -= 2) {
-            const float4 v = *reinterpret_cast<const float4*>(cp + b * 2);   // col b: (x,y), col b+1: (z,w)
+        for (int q = 0; q < RB; ++q)
 #pragma unroll
-            for (int q = 0; q < RB; ++q) {
-                uint32_t f1 = __float_as_uint(v.w - xi[q][1]), f0 = __float_as_uint(v.y - xi[q][1]);
-                if constexpr (K0 == 0) {
-                    f1 |= __float_as_uint(v.z - xi[q][0]);
-                    f0 |= __float_as_uint(v.x - xi[q][0]);
+            for (int g = 0; g < 4; ++g) a[q][g] = 0u;
+#pragma unroll
+        for (int h = 1; h >= 0; --h) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+                const float4 v = *reinterpret_cast<const float4*>(f1w + g * 8 + h * 4);
+#pragma unroll
+                for (int q = 0; q < RB; ++q) {
+                    a[q][g] = __funnelshift_l(__float_as_uint(v.w - xf1[q]), a[q][g], 1);
+                    a[q][g] = __funnelshift_l(__float_as_uint(v.z - xf1[q]), a[q][g], 1);
+                    a[q][g] = __funnelshift_l(__float_as_uint(v.y - xf1[q]), a[q][g], 1);
+                    a[q][g] = __funnelshift_l(__float_as_uint(v.x - xf1[q]), a[q][g], 1);
                 }
-                w[q] = __funnelshift_l(f1, w[q], 1);
-                w[q] = __funnelshift_l(f0, w[q], 1);
             }
         }
+#pragma unroll
+        for (int q = 0; q < RB; ++q) w[q] = a[q][0] | (a[q][1] << 8) | (a[q][2] << 16) | (a[q][3] << 24);
     } else {
 #pragma unroll
         for (int b = 31; b >= 0; --b) {
-            float cv[C];
-            load_col<C>(cp + b * C, cv);
+            float cv[CR];
+            load_col<CR>(restw + b * CR, cv);
+            const float c1 = F1 ? f1w[b] : 0.0f;
 #pragma unroll
             for (int q = 0; q < RB; ++q) {
-                uint32_t f = 0u;
+                uint32_t f = F1 ? __float_as_uint(c1 - xf1[q]) : 0u;
 #pragma unroll
-                for (int k = K0; k < C; ++k) f |= __float_as_uint(cv[k] - xi[q][k]);
+                for (int k = 0; k < CR; ++k) f |= __float_as_uint(cv[k] - xr[q][k]);
                 w[q] = __funnelshift_l(f, w[q], 1);   // (w << 1) | sign(f)
             }
         }
     }
 }
 
-// One CTA: TILE_WARPS x `slabs` slabs of SLAB dominator rows against one panel (TW columns).
-// Lane <-> row (RB rows per lane, values in registers); the panel's column values sit in shared
-// memory and are broadcast; each lane assembles its own 32-bit words.  Words are staged through
-// shared memory so the 128-byte panel rows leave as full coalesced lines, and the same pass over
-// the staged words feeds carry-save adders whose planes persist over the warp's slabs and become
-// the column counts.  M = objectives.  Off-diagonal CTAs stage objectives 1..M-1 (C = M-1 values
-// per point); the diagonal CTAs of a panel stage all M.
-template <int M, bool DIAG>
-__device__ __forceinline__ void tile_body(const float* __restrict__ ucols, int64_t npad, int U, int l, int J,
-                                          int col0, int row0, int rowlimit, int slabs, uint32_t* __restrict__ bits,
-                                          int* __restrict__ count, int world, int rank, uint32_t* smem) {
-    constexpr int C = DIAG ? M : (M > 1 ? M - 1 : 1);      // staged values per point
-    constexpr int KOFF = DIAG ? 0 : 1;                     // first staged objective
-    constexpr bool HAVE = DIAG || M > 1;                   // any objective staged at all
-    constexpr int NUP = 6;                                 // planes 8 .. 256 (MAX_SLABS * SLAB rows)
-    float* colv = reinterpret_cast<float*>(smem);                          // [TW][C]
-    uint32_t* stage = smem + M * TW;                                       // [TILE_WARPS][PW][SLAB+1]
-    int* scount = reinterpret_cast<int*>(stage + TILE_WARPS * PW * (SLAB + 1));   // [TW]
+// Columns of a word are in ascending f2: the pairs with f2_row <= f2_col form a suffix of the word.
+__device__ __forceinline__ uint32_t f2_mask(const float* c, float r) {
+    int pos = (c[15] < r) ? 16 : 0;
+    pos += (c[pos + 7] < r) ? 8 : 0;
+    pos += (c[pos + 3] < r) ? 4 : 0;
+    pos += (c[pos + 1] < r) ? 2 : 0;
+    pos += (c[pos] < r) ? 1 : 0;
+    if (pos == 31 && c[31] < r) pos = 32;
+    return pos >= 32 ? 0u : (0xFFFFFFFFu << pos);
+}
 
-    if constexpr (HAVE) {
-        for (int t = threadIdx.x; t < C * TW; t += blockDim.x) {
-            const int c = t / C, k = t - c * C;
-            colv[t] = ucols[(int64_t)(k + KOFF) * npad + col0 + c];
-        }
+constexpr int TILE_NUP = 6;                            // count planes 8 .. 256 (MAX_SLABS * SLAB rows)
+
+struct CountPlanes {
+    uint32_t ones = 0, twos = 0, fours = 0, up[TILE_NUP] = {0, 0, 0, 0, 0, 0};
+};
+
+// Copy one staged slab out (lane <-> word column: full 128-byte lines) and fold it into the planes.
+__device__ __forceinline__ void slab_out(const uint32_t* sl, uint32_t* gout, int lane, CountPlanes& cp) {
+    for (int rl = 0; rl < SLAB; rl += 8) {
+        uint32_t v[8];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) v[t] = sl[rl + t];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) gout[(int64_t)(rl + t) * PW + lane] = v[t];
+        uint32_t ta, tb, fa, fb, e;
+        csa(ta, cp.ones, cp.ones, v[0], v[1]);
+        csa(tb, cp.ones, cp.ones, v[2], v[3]);
+        csa(fa, cp.twos, cp.twos, ta, tb);
+        csa(ta, cp.ones, cp.ones, v[4], v[5]);
+        csa(tb, cp.ones, cp.ones, v[6], v[7]);
+        csa(fb, cp.twos, cp.twos, ta, tb);
+        csa(e, cp.fours, cp.fours, fa, fb);
+#pragma unroll
+        for (int p = 0; p < TILE_NUP; ++p) { const uint32_t c = cp.up[p] & e; cp.up[p] ^= e; e = c; }
     }
-    for (int t = threadIdx.x; t < TW; t += blockDim.x) scount[t] = 0;
-    __syncthreads();
+}
 
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t* st = stage + warp * PW * (SLAB + 1);
-    const uint32_t* sl = st + lane * (SLAB + 1);
-    uint32_t ones = 0, twos = 0, fours = 0, up[NUP];
-#pragma unroll
-    for (int p = 0; p < NUP; ++p) up[p] = 0;
-    bool any_rows = false;
-
-    for (int sidx = 0; sidx < slabs; ++sidx) {
-        const int rs = row0 + (sidx * TILE_WARPS + warp) * SLAB;            // first row of this slab
-        if (rs >= rowlimit) break;                                          // warp-uniform
-        any_rows = true;
-        float xi[RB][C];
-#pragma unroll
-        for (int q = 0; q < RB; ++q)
-#pragma unroll
-            for (int k = 0; k < C; ++k)
-                xi[q][k] = HAVE ? ucols[(int64_t)(k + KOFF) * npad + rs + q * 32 + lane] : 0.0f;
-        // f1 range of the slab (rows are f1-sorted inside their block): first and last valid row
-        float rmin = 0.f, rmax = 0.f;
-        if constexpr (!DIAG && M > 1) {
-            const int last = min(rs + SLAB, rowlimit) - 1 - rs;             // >= 0
-            rmin = __shfl_sync(0xFFFFFFFFu, xi[0][0], 0);
-            float cand = xi[0][0];
-#pragma unroll
-            for (int q = 1; q < RB; ++q) cand = ((last >> 5) == q) ? xi[q][0] : cand;
-            rmax = __shfl_sync(0xFFFFFFFFu, cand, last & 31);
-        }
-
-        for (int wc = 0; wc < PW; ++wc) {
-            const int cb = col0 + wc * 32;                              // first column of this word
-            uint32_t w[RB];
-            const float* cp = colv + wc * 32 * C;
-            const int ncol = min(32, U - cb);                           // valid columns in this word
-            if (ncol <= 0) {
-#pragma unroll
-                for (int q = 0; q < RB; ++q) w[q] = 0u;
-            } else {
-                if constexpr (DIAG) {
-#pragma unroll
-                    for (int q = 0; q < RB; ++q) w[q] = 0u;
-#pragma unroll
-                    for (int b = 0; b < 32; ++b) {
-                        float cv[C];
-                        load_col<C>(cp + b * C, cv);
-#pragma unroll
-                        for (int q = 0; q < RB; ++q) {
-                            bool p = true;
-#pragma unroll
-                            for (int k = 0; k < C; ++k) p = p && (xi[q][k] <= cv[k]);
-                            if (p) w[q] |= (1u << b);
-                        }
-                    }
-#pragma unroll
-                    for (int q = 0; q < RB; ++q) {                      // unique rows: only i == j is "equal"
-                        const int d = rs + q * 32 + lane - cb;
-                        if (d >= 0 && d < 32) w[q] &= ~(1u << d);
-                    }
-                } else if constexpr (M == 1) {
-#pragma unroll
-                    for (int q = 0; q < RB; ++q) w[q] = 0xFFFFFFFFu;    // lower block: f0 <= by order
-                } else {
-                    const float cmin = cp[0], cmax = cp[(ncol - 1) * C];
-                    if (rmin > cmax) {                                  // every row's f1 > every column's
-#pragma unroll
-                        for (int q = 0; q < RB; ++q) w[q] = 0u;
-                    } else {
-                        if (rmax <= cmin) word_sign<C, 1>(cp, xi, w);   // f1 passes for every pair
-                        else word_sign<C, 0>(cp, xi, w);
-#pragma unroll
-                        for (int q = 0; q < RB; ++q) w[q] = ~w[q];      // fail bits -> pass bits
-                    }
-                }
-                const uint32_t cmask = (ncol >= 32) ? 0xFFFFFFFFu : ((1u << ncol) - 1u);
-#pragma unroll
-                for (int q = 0; q < RB; ++q) w[q] = (rs + q * 32 + lane < U) ? (w[q] & cmask) : 0u;
-            }
-#pragma unroll
-            for (int q = 0; q < RB; ++q) st[wc * (SLAB + 1) + q * 32 + lane] = w[q];
-        }
-        __syncwarp();
-
-        // copy-out (lane <-> word column) fused with the vertical popcount of the slab
-        uint32_t* gout = bits + d_panel_words_before(l, world, rank) + (int64_t)rs * PW;
-        for (int rl = 0; rl < SLAB; rl += 8) {
-            uint32_t v[8];
-#pragma unroll
-            for (int t = 0; t < 8; ++t) v[t] = sl[rl + t];
-#pragma unroll
-            for (int t = 0; t < 8; ++t) gout[(int64_t)(rl + t) * PW + lane] = v[t];
-            uint32_t ta, tb, fa, fb, e;
-            csa(ta, ones, ones, v[0], v[1]);
-            csa(tb, ones, ones, v[2], v[3]);
-            csa(fa, twos, twos, ta, tb);
-            csa(ta, ones, ones, v[4], v[5]);
-            csa(tb, ones, ones, v[6], v[7]);
-            csa(fb, twos, twos, ta, tb);
-            csa(e, fours, fours, fa, fb);
-#pragma unroll
-            for (int p = 0; p < NUP; ++p) { const uint32_t c = up[p] & e; up[p] ^= e; e = c; }
-        }
-        __syncwarp();
-    }
+// Planes -> per-column integers in shared memory -> one global atomic per non-zero column.
+__device__ __forceinline__ void counts_flush(const CountPlanes& cp, bool any_rows, int lane, int* scount,
+                                             int* __restrict__ count, int l) {
     if (any_rows) {
 #pragma unroll 4
         for (int bb = 0; bb < 32; ++bb) {
             const int bit = (bb + lane) & 31;
-            int v = ((ones >> bit) & 1) | (((twos >> bit) & 1) << 1) | (((fours >> bit) & 1) << 2);
+            int v = ((cp.ones >> bit) & 1) | (((cp.twos >> bit) & 1) << 1) | (((cp.fours >> bit) & 1) << 2);
 #pragma unroll
-            for (int p = 0; p < NUP; ++p) v |= ((up[p] >> bit) & 1) << (3 + p);
+            for (int p = 0; p < TILE_NUP; ++p) v |= ((cp.up[p] >> bit) & 1) << (3 + p);
             if (v) atomicAdd(&scount[lane * 32 + bit], v);
         }
     }
@@ -423,6 +357,188 @@ __device__ __forceinline__ void tile_body(const float* __restrict__ ucols, int64
         const int v = scount[t];
         if (v) atomicAdd(&count[(int64_t)l * TW + t], v);
     }
+}
+
+// ---- off-diagonal CTA: rows of a lower block against one panel ------------------------------------
+// Lane <-> row (RB rows per lane, values in registers); the panel's column values sit in shared
+// memory (f1 and f2 as separate arrays, objectives 3.. interleaved) and are broadcast.  Two passes
+// per 64-row slab.  Pass 1, every word: classify by f1 range (skip / f1 passes / mixed), and for the
+// words not skipped find the f2 suffix mask by binary search - the iterations are independent, so
+// four searches are in flight per lane.  Pass 2, only the words that still need compares: fail bits
+// on the FMA pipe, AND-ed into the staged word.  Then the slab leaves as full 128-byte lines while
+// carry-save adders accumulate the column counts.
+template <int M>
+__device__ __forceinline__ void tile_offdiag(const float* __restrict__ ucols, int64_t npad, int U, int l, int col0,
+                                             int row0, int rowlimit, int slabs, uint32_t* __restrict__ bits,
+                                             int* __restrict__ count, int world, int rank, uint32_t* smem) {
+    constexpr int CR = (M > 3) ? M - 3 : 0;
+    float* f1s = reinterpret_cast<float*>(smem);                           // [TW]
+    float* f2s = f1s + TW;                                                 // [TW]
+    float* rest = f2s + TW;                                                // [TW][CR]
+    uint32_t* stage = smem + M * TW;                                       // [TILE_WARPS][PW][SLAB+1]
+    int* scount = reinterpret_cast<int*>(stage + TILE_WARPS * PW * (SLAB + 1));   // [TW]
+    float* wmin = reinterpret_cast<float*>(scount + TW);                   // [PW] f1 range of each word
+    float* wmax = wmin + PW;
+
+    for (int t = threadIdx.x; t < TW; t += blockDim.x) {
+        if constexpr (M >= 2) f1s[t] = ucols[npad + col0 + t];
+        if constexpr (M >= 3) f2s[t] = ucols[2 * npad + col0 + t];
+#pragma unroll
+        for (int k = 0; k < CR; ++k) rest[t * CR + k] = ucols[(int64_t)(3 + k) * npad + col0 + t];
+        scount[t] = 0;
+    }
+    __syncthreads();
+    if constexpr (M >= 2) {
+        if (threadIdx.x < PW) {
+            float lo = INFINITY, hi = -INFINITY;
+            for (int c = 0; c < 32; ++c) {                                  // fminf / fmaxf skip the NaN padding
+                const float v = f1s[threadIdx.x * 32 + c];
+                lo = fminf(lo, v);
+                hi = fmaxf(hi, v);
+            }
+            wmin[threadIdx.x] = lo;
+            wmax[threadIdx.x] = hi;
+        }
+        __syncthreads();
+    }
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t* st = stage + warp * PW * (SLAB + 1);
+    CountPlanes cp;
+    bool any_rows = false;
+
+    for (int sidx = 0; sidx < slabs; ++sidx) {
+        const int rs = row0 + (sidx * TILE_WARPS + warp) * SLAB;            // first row of this slab
+        if (rs >= rowlimit) break;                                          // warp-uniform
+        any_rows = true;
+        float xf1[RB], xf2[RB], xr[RB][CR > 0 ? CR : 1];
+#pragma unroll
+        for (int q = 0; q < RB; ++q) {
+            const int64_t i = rs + q * 32 + lane;                           // rows of a lower block: all valid
+            xf1[q] = (M >= 2) ? ucols[npad + i] : 0.0f;
+            xf2[q] = (M >= 3) ? ucols[2 * npad + i] : 0.0f;
+#pragma unroll
+            for (int k = 0; k < CR; ++k) xr[q][k] = ucols[(int64_t)(3 + k) * npad + i];
+        }
+        float rmin = xf1[0], rmax = xf1[0];                                 // f1 range of the slab
+#pragma unroll
+        for (int q = 1; q < RB; ++q) { rmin = fminf(rmin, xf1[q]); rmax = fmaxf(rmax, xf1[q]); }
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) {
+            rmin = fminf(rmin, __shfl_xor_sync(0xFFFFFFFFu, rmin, o));
+            rmax = fmaxf(rmax, __shfl_xor_sync(0xFFFFFFFFu, rmax, o));
+        }
+
+        uint32_t need_full = 0u, need_rest = 0u;                            // warp-uniform word sets
+#pragma unroll 4
+        for (int wc = 0; wc < PW; ++wc) {
+            const int ncol = min(32, U - (col0 + wc * 32));                 // valid columns in this word
+            const uint32_t cmask = (ncol >= 32) ? 0xFFFFFFFFu : (ncol <= 0 ? 0u : ((1u << ncol) - 1u));
+            bool skip = ncol <= 0, f1pass = true;
+            if constexpr (M >= 2) {
+                skip = skip || (rmin > wmax[wc]);                           // every row's f1 > every column's
+                f1pass = rmax <= wmin[wc];                                  // f1 passes for every pair
+            }
+#pragma unroll
+            for (int q = 0; q < RB; ++q) {
+                uint32_t m = 0u;
+                if (!skip) m = ((M >= 3) ? f2_mask(f2s + wc * 32, xf2[q]) : 0xFFFFFFFFu) & cmask;
+                st[wc * (SLAB + 1) + q * 32 + lane] = m;
+            }
+            if (!skip) {
+                if (!f1pass) need_full |= 1u << wc;
+                else if (CR > 0) need_rest |= 1u << wc;
+            }
+        }
+        while (need_full) {
+            const int wc = __ffs(need_full) - 1;
+            need_full &= need_full - 1;
+            uint32_t f[RB];
+            word_fail<CR, true>(f1s + wc * 32, rest + wc * 32 * CR, xf1, xr, f);
+#pragma unroll
+            for (int q = 0; q < RB; ++q) st[wc * (SLAB + 1) + q * 32 + lane] &= ~f[q];
+        }
+        if constexpr (CR > 0) {
+            while (need_rest) {
+                const int wc = __ffs(need_rest) - 1;
+                need_rest &= need_rest - 1;
+                uint32_t f[RB];
+                word_fail<CR, false>(f1s + wc * 32, rest + wc * 32 * CR, xf1, xr, f);
+#pragma unroll
+                for (int q = 0; q < RB; ++q) st[wc * (SLAB + 1) + q * 32 + lane] &= ~f[q];
+            }
+        }
+        __syncwarp();
+        slab_out(st + lane * (SLAB + 1), bits + d_panel_words_before(l, world, rank) + (int64_t)rs * PW, lane, cp);
+        __syncwarp();
+    }
+    counts_flush(cp, any_rows, lane, scount, count, l);
+}
+
+// ---- diagonal CTA: a block against its own panel ---------------------------------------------------
+// Either direction may dominate inside a block, so all M objectives are tested (FSETP chain) and
+// only i == j is excluded (rows are unique).  1/NP of the work.
+template <int M>
+__device__ __forceinline__ void tile_diag(const float* __restrict__ ucols, int64_t npad, int U, int l, int col0,
+                                          int row0, int rowlimit, int slabs, uint32_t* __restrict__ bits,
+                                          int* __restrict__ count, int world, int rank, uint32_t* smem) {
+    float* colv = reinterpret_cast<float*>(smem);                          // [TW][M]
+    uint32_t* stage = smem + M * TW;
+    int* scount = reinterpret_cast<int*>(stage + TILE_WARPS * PW * (SLAB + 1));
+    for (int t = threadIdx.x; t < M * TW; t += blockDim.x) {
+        const int c = t / M, k = t - c * M;
+        colv[t] = ucols[(int64_t)k * npad + col0 + c];
+    }
+    for (int t = threadIdx.x; t < TW; t += blockDim.x) scount[t] = 0;
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t* st = stage + warp * PW * (SLAB + 1);
+    CountPlanes cp;
+    bool any_rows = false;
+    for (int sidx = 0; sidx < slabs; ++sidx) {
+        const int rs = row0 + (sidx * TILE_WARPS + warp) * SLAB;
+        if (rs >= rowlimit) break;
+        any_rows = true;
+        float xi[RB][M];
+#pragma unroll
+        for (int q = 0; q < RB; ++q)
+#pragma unroll
+            for (int k = 0; k < M; ++k) xi[q][k] = ucols[(int64_t)k * npad + rs + q * 32 + lane];
+        for (int wc = 0; wc < PW; ++wc) {
+            const int cb = col0 + wc * 32;
+            const int ncol = min(32, U - cb);
+            uint32_t w[RB];
+#pragma unroll
+            for (int q = 0; q < RB; ++q) w[q] = 0u;
+            if (ncol > 0) {
+                const float* cpw = colv + wc * 32 * M;
+#pragma unroll
+                for (int b = 0; b < 32; ++b) {
+                    float cv[M];
+                    load_col<M>(cpw + b * M, cv);
+#pragma unroll
+                    for (int q = 0; q < RB; ++q) {
+                        bool p = true;
+#pragma unroll
+                        for (int k = 0; k < M; ++k) p = p && (xi[q][k] <= cv[k]);   // NaN padding never passes
+                        if (p) w[q] |= (1u << b);
+                    }
+                }
+#pragma unroll
+                for (int q = 0; q < RB; ++q) {                          // unique rows: only i == j is "equal"
+                    const int d = rs + q * 32 + lane - cb;
+                    if (d >= 0 && d < 32) w[q] &= ~(1u << d);
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < RB; ++q) st[wc * (SLAB + 1) + q * 32 + lane] = w[q];
+        }
+        __syncwarp();
+        slab_out(st + lane * (SLAB + 1), bits + d_panel_words_before(l, world, rank) + (int64_t)rs * PW, lane, cp);
+        __syncwarp();
+    }
+    counts_flush(cp, any_rows, lane, scount, count, l);
 }
 
 template <int M>
@@ -438,10 +554,8 @@ k_dominance_tiles(const float* __restrict__ ucols, int64_t npad, const Scal* __r
     const int row0 = blockIdx.x * (slabs * TILE_WARPS * SLAB);
     if (row0 >= rowlimit) return;
     extern __shared__ __align__(16) uint32_t smem[];
-    if (row0 >= col0)
-        tile_body<M, true>(ucols, npad, U, l, J, col0, row0, rowlimit, slabs, bits, count, world, rank, smem);
-    else
-        tile_body<M, false>(ucols, npad, U, l, J, col0, row0, rowlimit, slabs, bits, count, world, rank, smem);
+    if (row0 >= col0) tile_diag<M>(ucols, npad, U, l, col0, row0, rowlimit, slabs, bits, count, world, rank, smem);
+    else tile_offdiag<M>(ucols, npad, U, l, col0, row0, rowlimit, slabs, bits, count, world, rank, smem);
 }
 
 // Fallback for M > MAX_TEMPLATE_M: same labelling and layout, objective loop at run time.
@@ -850,7 +964,7 @@ struct Plan {
 template <int M>
 static int launch_tiles(const Plan& P, cudaStream_t s) {
     const Layout& L = P.L;
-    const size_t smem = sizeof(uint32_t) * ((size_t)M * TW + (size_t)TILE_WARPS * PW * (SLAB + 1) + TW);
+    const size_t smem = sizeof(uint32_t) * ((size_t)M * TW + (size_t)TILE_WARPS * PW * (SLAB + 1) + TW + 2 * PW);
     EVX_CUDA(cudaFuncSetAttribute(k_dominance_tiles<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     // rows per CTA = slabs * TILE_WARPS * SLAB (256 .. 1024, always dividing TW): as many passes per
     // warp as still leave a few waves of CTAs on the chip
@@ -906,6 +1020,14 @@ static int build(const Plan& P, const float* x, cudaStream_t s, cudaEvent_t tile
         size_t tb2 = L.cubtmp_bytes;
         EVX_CUDA(cub::DeviceRadixSort::SortPairs(P.at<void>(L.cubtmp), tb2, P.at<uint64_t>(L.bkeyA),
                                                  P.at<uint64_t>(L.bkeyB), idx_cur, idx_nxt, (int)n, 0, 32 + bbits, s));
+        if (m >= 3) {                                  // word-local f2 order
+            k_word_keys<<<gn, T, 0, s>>>(P.at<float>(L.tcols), idx_nxt, n, L.npad, L.np, scal, P.at<uint64_t>(L.bkeyA));
+            EVX_LAUNCH_CHECK();
+            tb2 = L.cubtmp_bytes;
+            EVX_CUDA(cub::DeviceRadixSort::SortPairs(P.at<void>(L.cubtmp), tb2, P.at<uint64_t>(L.bkeyA),
+                                                     P.at<uint64_t>(L.bkeyB), idx_nxt, idx_cur, (int)n, 0, 32 + bbits + 5, s));
+            int* t = idx_cur; idx_cur = idx_nxt; idx_nxt = t;
+        }
         k_block_permute<<<gn, T, 0, s>>>(P.at<float>(L.tcols), idx_nxt, n, L.npad, m, scal, P.at<float>(L.ucols),
                                          P.at<int>(L.label));
         EVX_LAUNCH_CHECK();
