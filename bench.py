@@ -35,6 +35,8 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-sample", type=int, default=0, help="rows of the CPU-baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
+                    help="multi-GPU front exchange: in-kernel peer stores (default) or one NCCL all-gather per front")
     ap.add_argument("--no-nsga2", action="store_true", help="skip the NSGA-II generations/s side measurement")
     return ap.parse_args()
 
@@ -227,8 +229,8 @@ def run_ours(args):
         ms_e2e = timed(step_e2e, K)
         assert bool((rank_host.cuda() == rank_out).all()), "host and device entry points disagree"
     else:
-        from evox_b200.distributed import ShardedNonDominatedSort
-        sh = ShardedNonDominatedSort(n, m)
+        from evox_b200.distributed import FusedShardedNonDominatedSort, ShardedNonDominatedSort
+        sh = (ShardedNonDominatedSort if args.exchange == "nccl" else FusedShardedNonDominatedSort)(n, m)
         for _ in range(W):
             sh(x)
         sampler = ClockSampler(local)
@@ -260,7 +262,7 @@ def run_ours(args):
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": workload_name(n, m), "fronts": fronts, "parallelism": f"column-panel shards x{world}",
+            "config": {"workload": workload_name(n, m), "fronts": fronts, "parallelism": f"column-panel shards x{world}" + (f", front exchange: {args.exchange}" if world > 1 else ""),
                        "l2": "working set (packed bit matrix %.1f GB) >> 126 MB L2; no flush needed" % (n * n / 16 / 1e9)},
             "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": pairs * K / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": n * m * 4,

@@ -46,13 +46,15 @@ struct Scal {
     int nf3[3];     // persistent peel: front sizes, triple buffered (read k, append k+1, clear k+2)
     int fronts;     // persistent peel: number of fronts found
     unsigned int barrier;   // persistent peel: grid barrier arrivals (monotonic)
+    unsigned int go;        // fused multi-rank peel: release word written by CTA 0
+    int abort;              // fused multi-rank peel: a peer barrier timed out
 };
 
 struct Layout {
     int64_t n, npad;
     int m, world, rank, np, npl, npl_max;
     size_t keys, idxA, idxB, skeyA, skeyB, flags, incl, cubtmp, cubtmp_bytes, ucols, row2u, count,
-        rank_u, flist, flist2, cplanes, mask, scal, bits, total, tcols, bkeyA, bkeyB, label;
+        rank_u, flist, flist2, cplanes, mask, scal, bits, total, tcols, bkeyA, bkeyB, label, fmask;
     int kplanes;
     int64_t bits_words;
 };
@@ -108,6 +110,7 @@ static Layout make_layout(int64_t n, int m, int world, int rank) {
     L.kplanes = 1;
     while ((1ll << L.kplanes) <= L.npad) ++L.kplanes;          // counts < npad fit in kplanes bits
     L.cplanes = take(sizeof(uint32_t) * (size_t)L.npl_max * (L.kplanes + 1) * PW);
+    L.fmask = take(sizeof(uint32_t) * 2 * (size_t)(L.npad / 32));   // front membership, double buffered
     L.mask = take(sizeof(uint32_t) * (size_t)L.npl_max * PW * world);
     L.scal = take(sizeof(Scal));
     L.bits_words = panel_words_before(L.npl, world, rank);
@@ -734,6 +737,134 @@ struct PeelShared {
     int nf;
 };
 
+// ---- peer-visible state of the fused multi-rank peel ------------------------------------------------
+// Every rank provides one buffer in peer-mapped memory (torch symmetric memory / CUDA IPC):
+// [PeerState | flistA npad ints | flistB npad ints].  Publishers write new front members straight
+// into EVERY rank's list over NVLink and bump every rank's counter with a system-scope atomic; the
+// per-front barrier spans all CTAs of all ranks (local arrive -> flags to peers -> local release).
+constexpr int MAX_WORLD = 8;
+struct PeerState {
+    int nf3[3];
+    int abort;
+    unsigned int xflag[MAX_WORLD];
+    unsigned int pad[52];
+};
+static_assert(sizeof(PeerState) == 256, "PeerState must stay 256 bytes");
+struct PeerTable {
+    char* base[MAX_WORLD];
+    int world, rank;
+    int64_t npad;
+};
+__device__ __forceinline__ PeerState* peer_state(const PeerTable& pt, int r) {
+    return reinterpret_cast<PeerState*>(pt.base[r]);
+}
+__device__ __forceinline__ int* peer_flist(const PeerTable& pt, int r, int which) {
+    return reinterpret_cast<int*>(pt.base[r] + sizeof(PeerState)) + (size_t)which * pt.npad;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+constexpr unsigned long long PEER_TIMEOUT_NS = 4000000000ull;      // a peer that is 4 s late is gone
+
+// Barrier over all CTAs of all ranks.  Returns the size of the next front, or -1 after a time-out
+// (every rank then leaves the kernel; nothing spins forever).
+__device__ __forceinline__ int world_barrier(Scal* scal, unsigned int& epoch, const PeerTable& pt, int nf_slot,
+                                             int* nf_smem) {
+    __syncthreads();
+    ++epoch;
+    if (threadIdx.x == 0) {
+        PeerState* me = peer_state(pt, pt.rank);
+        const unsigned long long t0 = global_ns();
+        bool dead = false;
+        __threadfence_system();
+        atomicAdd(&scal->barrier, 1u);
+        if (blockIdx.x == 0) {
+            unsigned int v;
+            do {                                                      // every local CTA has arrived
+                asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&scal->barrier) : "memory");
+            } while (v < epoch * gridDim.x);
+            __threadfence_system();
+            for (int r = 0; r < pt.world; ++r)                        // tell every rank (and myself)
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(&peer_state(pt, r)->xflag[pt.rank]), "r"(epoch)
+                             : "memory");
+            for (int r = 0; r < pt.world && !dead; ++r) {             // wait for every rank
+                do {
+                    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(&me->xflag[r]) : "memory");
+                    int ab;
+                    asm volatile("ld.relaxed.sys.global.s32 %0, [%1];" : "=r"(ab) : "l"(&me->abort) : "memory");
+                    if (ab || global_ns() - t0 > PEER_TIMEOUT_NS) dead = true;
+                } while (v < epoch && !dead);
+            }
+            if (dead) {
+                for (int r = 0; r < pt.world; ++r)
+                    asm volatile("st.relaxed.sys.global.s32 [%0], %1;" ::"l"(&peer_state(pt, r)->abort), "r"(1) : "memory");
+                scal->abort = 1;
+            }
+            __threadfence();
+            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&scal->go), "r"(epoch) : "memory");
+        } else {
+            unsigned int v;
+            do {
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&scal->go) : "memory");
+            } while (v < epoch && global_ns() - t0 < 2 * PEER_TIMEOUT_NS);
+            if (v < epoch) dead = true;
+        }
+        int ab;
+        asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(ab) : "l"(&scal->abort) : "memory");
+        int nf;
+        asm volatile("ld.relaxed.sys.global.s32 %0, [%1];" : "=r"(nf) : "l"(&me->nf3[nf_slot]) : "memory");
+        *nf_smem = (dead || ab) ? -1 : nf;
+    }
+    __syncthreads();
+    return *nf_smem;
+}
+
+// Warp 0, multi-rank: subtract, detect, retire, and append the new front members to every rank's list.
+__device__ __forceinline__ void peel_commit_world(uint32_t* cp, int K, const uint32_t (*delta)[32], int pm, int lane,
+                                                  int J, const PeerTable& pt, int which_next, int nf_slot,
+                                                  uint32_t* newmask_out) {
+    uint32_t borrow = 0, nz = 0;
+    for (int p = 0; p < K; ++p) {
+        const uint32_t c = cp[p * PW + lane];
+        const uint32_t d = (p < pm) ? delta[p][lane] : 0u;
+        const uint32_t x = c ^ d;
+        const uint32_t r = x ^ borrow;
+        borrow = (~c & d) | (~x & borrow);
+        if (pm > 0) cp[p * PW + lane] = r;
+        nz |= r;
+    }
+    uint32_t alive = cp[K * PW + lane];
+    const uint32_t nw = alive & ~nz;
+    alive &= ~nw;
+    cp[K * PW + lane] = alive;
+    newmask_out[lane] = nw;
+    const int c = __popc(nw);
+    int incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    const int total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+    if (total == 0) return;                                           // warp-uniform
+    int mybase = 0;                                                   // lane r reserves the slots on rank r
+    if (lane < pt.world) mybase = atomicAdd_system(&peer_state(pt, lane)->nf3[nf_slot], total);
+    const int col0 = J * TW + lane * 32;
+    for (int r = 0; r < pt.world; ++r) {
+        int base = __shfl_sync(0xFFFFFFFFu, mybase, r) + incl - c;
+        int* dst = peer_flist(pt, r, which_next);
+        uint32_t w = nw;
+        while (w) {
+            const int b = __ffs(w) - 1;
+            w &= w - 1;
+            dst[base++] = col0 + b;                                   // posted store over NVLink for r != rank
+        }
+    }
+    __threadfence_system();
+}
+
 // Grid-wide barrier on a monotonically increasing counter (all CTAs are co-resident: cooperative
 // launch).  `epoch` counts the barriers this CTA has passed.  Only thread 0 touches global memory:
 // it also fetches the size of the front about to be processed, so 4 700 warps do not all hit the
@@ -817,10 +948,16 @@ __device__ __forceinline__ void csa8(uint32_t& ones, uint32_t& twos, uint32_t& f
     }
 }
 
+template <bool MULTI>
 __global__ void __launch_bounds__(PEEL_WARPS * 32, 2)
 k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ count, int* __restrict__ rank_u,
                   int* flistA, int* flistB, Scal* scal, uint32_t* __restrict__ cplanes, int npl, int K, int world,
-                  int rank, int planes_in_smem) {
+                  int rank, int planes_in_smem, PeerTable pt) {
+    if constexpr (MULTI) {                                            // lists and counters live in the peer buffer
+        flistA = peer_flist(pt, pt.rank, 0);
+        flistB = peer_flist(pt, pt.rank, 1);
+    }
+    int* const nf3 = MULTI ? peer_state(pt, pt.rank)->nf3 : scal->nf3;
     extern __shared__ __align__(16) unsigned char peel_smem_raw[];
     PeelShared& sh = *reinterpret_cast<PeelShared*>(peel_smem_raw);
     uint32_t* cp_smem = reinterpret_cast<uint32_t*>(peel_smem_raw + sizeof(PeelShared));
@@ -849,19 +986,22 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
             if (lane == 0) cp[K * PW + (c >> 5)] = a;
         }
         __syncthreads();
-        if (warp == 0) peel_commit(cp, K, nullptr, 0, lane, J, flistA, &scal->nf3[0], sh.newmask);
+        if (warp == 0) {
+            if constexpr (MULTI) peel_commit_world(cp, K, nullptr, 0, lane, J, pt, 0, 0, sh.newmask);
+            else peel_commit(cp, K, nullptr, 0, lane, J, flistA, &nf3[0], sh.newmask);
+        }
         __syncthreads();
         for (int c = threadIdx.x; c < TW; c += blockDim.x)
             if ((sh.newmask[c >> 5] >> (c & 31)) & 1u) rank_u[(size_t)l * TW + c] = 0;
         __syncthreads();
     }
-    int nf = grid_barrier(bar, epoch, &scal->nf3[0], &sh.nf);
+    int nf = MULTI ? world_barrier(scal, epoch, pt, 0, &sh.nf) : grid_barrier(bar, epoch, &nf3[0], &sh.nf);
 
     // ---- fronts ----------------------------------------------------------------------------------
     int k = 0;
     for (;; ++k) {
-        if (nf == 0) break;
-        if (B == 0 && threadIdx.x == 0) scal->nf3[(k + 2) % 3] = 0;
+        if (nf <= 0) break;
+        if (B == 0 && threadIdx.x == 0) nf3[(k + 2) % 3] = 0;
         const int* fl = (k & 1) ? flistB : flistA;
         int* fl_next = (k & 1) ? flistA : flistB;
         for (int q0 = 0, slot = 0; q0 < npl; q0 += G, ++slot) {
@@ -926,8 +1066,225 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
                     }
                     __syncthreads();
                 }
+                if (warp == 0) {
+                    if constexpr (MULTI)
+                        peel_commit_world(cp, K, sh.merge[0], pm, lane, J, pt, (k + 1) & 1, (k + 1) % 3, sh.newmask);
+                    else
+                        peel_commit(cp, K, sh.merge[0], pm, lane, J, fl_next, &nf3[(k + 1) % 3], sh.newmask);
+                }
+                __syncthreads();
+                for (int c = threadIdx.x; c < TW; c += blockDim.x)
+                    if ((sh.newmask[c >> 5] >> (c & 31)) & 1u) rank_u[(size_t)l * TW + c] = k + 1;
+                __syncthreads();
+            }
+        }
+        nf = MULTI ? world_barrier(scal, epoch, pt, (k + 1) % 3, &sh.nf)
+                   : grid_barrier(bar, epoch, &nf3[(k + 1) % 3], &sh.nf);
+    }
+    if (B == 0 && threadIdx.x == 0) scal->fronts = (nf < 0) ? -1 : k;
+}
+
+// ------------------------------------------------------------------------------------------------
+// stage 3c: persistent peel driven by front MASKS (default single-rank path)
+// ------------------------------------------------------------------------------------------------
+// Same ownership, bit-sliced counts and merge as k_peel_persistent, but a front is published as its
+// membership bit mask (one 128-byte store per panel, no list, no slot atomics), and a panel's owner
+// scans only the mask words below its row limit, so rows that have no storage in the panel are never
+// visited.  Row segments are gathered with cp.async into a per-warp ring in shared memory (4 batches
+// of 8 rows in flight per warp, independent of registers) and consumed by the carry-save adders one
+// batch behind.
+constexpr int PEEL_DEPTH = 4;
+
+struct PeelSharedM {
+    uint32_t merge[PEEL_WARPS][PEEL_PM][32];
+    uint32_t ring[PEEL_WARPS][PEEL_DEPTH * 8][32];
+    uint32_t newmask[32];
+    int nf;
+};
+
+__device__ __forceinline__ void cp_async4(uint32_t* smem_dst, const uint32_t* gsrc) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// Warp 0: subtract, detect, retire, publish the panel's 32 mask words for the next front.
+__device__ __forceinline__ void peel_commit_mask(uint32_t* cp, int K, const uint32_t (*delta)[32], int pm, int lane,
+                                                 uint32_t* fmask_next_panel, bool first_pass, int* nf_next,
+                                                 uint32_t* newmask_out) {
+    uint32_t borrow = 0, nz = 0;
+    for (int p = 0; p < K; ++p) {
+        const uint32_t c = cp[p * PW + lane];
+        const uint32_t d = (p < pm) ? delta[p][lane] : 0u;
+        const uint32_t x = c ^ d;
+        const uint32_t r = x ^ borrow;
+        borrow = (~c & d) | (~x & borrow);
+        if (pm > 0) cp[p * PW + lane] = r;
+        nz |= r;
+    }
+    uint32_t alive = cp[K * PW + lane];
+    const uint32_t nw = alive & ~nz;
+    alive &= ~nw;
+    cp[K * PW + lane] = alive;
+    newmask_out[lane] = nw;
+    // one coalesced 128-byte store; later passes of the same front add to what the first one wrote
+    fmask_next_panel[lane] = first_pass ? nw : (fmask_next_panel[lane] | nw);
+    int total = __popc(nw);
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) total += __shfl_xor_sync(0xFFFFFFFFu, total, o);
+    if (lane == 0 && total) atomicAdd(nf_next, total);              // result unused: a fire-and-forget RED
+}
+
+__global__ void __launch_bounds__(PEEL_WARPS * 32, 2)
+k_peel_masks(const uint32_t* __restrict__ bits, const int* __restrict__ count, int* __restrict__ rank_u,
+             uint32_t* fmask, int64_t mask_words, Scal* scal, uint32_t* __restrict__ cplanes, int npl, int K, int world,
+             int rank, int planes_in_smem) {
+    extern __shared__ __align__(16) unsigned char peel_smem_raw[];
+    PeelSharedM& sh = *reinterpret_cast<PeelSharedM*>(peel_smem_raw);
+    uint32_t* cp_smem = reinterpret_cast<uint32_t*>(peel_smem_raw + sizeof(PeelSharedM));
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int G = gridDim.x, B = blockIdx.x;
+    const int U = scal->U;
+    const size_t cp_stride = (size_t)(K + 1) * PW;
+    unsigned int epoch = 0;
+    unsigned int* bar = reinterpret_cast<unsigned int*>(&scal->barrier);
+
+    // ---- init: int counts -> planes, alive mask, front 0 -----------------------------------------
+    for (int q0 = 0, slot = 0; q0 < npl; q0 += G, ++slot) {
+        const int q = q0 + ((slot & 1) ? (G - 1 - B) : B);
+        if (q >= npl) continue;                                     // CTA-uniform
+        const int l = peel_owner_panel(q, npl);
+        const int J = l * world + rank;
+        uint32_t* cp = planes_in_smem ? cp_smem + slot * cp_stride : cplanes + (size_t)l * cp_stride;
+        for (int c = threadIdx.x; c < TW; c += blockDim.x) {
+            const int j = J * TW + c;
+            const int v = (j < U) ? count[(size_t)l * TW + c] : 0;
+            for (int p = 0; p < K; ++p) {
+                const uint32_t w = __ballot_sync(0xFFFFFFFFu, (v >> p) & 1);
+                if (lane == 0) cp[p * PW + (c >> 5)] = w;
+            }
+            const uint32_t a = __ballot_sync(0xFFFFFFFFu, j < U);
+            if (lane == 0) cp[K * PW + (c >> 5)] = a;
+        }
+        __syncthreads();
+        if (warp == 0)
+            peel_commit_mask(cp, K, nullptr, 0, lane, fmask + (size_t)J * PW, true, &scal->nf3[0], sh.newmask);
+        __syncthreads();
+        for (int c = threadIdx.x; c < TW; c += blockDim.x)
+            if ((sh.newmask[c >> 5] >> (c & 31)) & 1u) rank_u[(size_t)l * TW + c] = 0;
+        __syncthreads();
+    }
+    int nf = grid_barrier(bar, epoch, &scal->nf3[0], &sh.nf);
+
+    // ---- fronts ----------------------------------------------------------------------------------
+    int k = 0;
+    uint32_t* ring = &sh.ring[warp][0][0];
+    for (;; ++k) {
+        if (nf == 0) break;
+        if (B == 0 && threadIdx.x == 0) scal->nf3[(k + 2) % 3] = 0;
+        const uint32_t* fm = fmask + (size_t)(k & 1) * mask_words;
+        uint32_t* fm_next = fmask + (size_t)((k + 1) & 1) * mask_words;
+        // a warp sees at most min(nf, rows it scans) rows per pass: keep that below the 12 planes
+        const bool one_pass = nf <= PEEL_ROWS_PER_WARP;
+        for (int q0 = 0, slot = 0; q0 < npl; q0 += G, ++slot) {
+            const int q = q0 + ((slot & 1) ? (G - 1 - B) : B);
+            if (q >= npl) continue;
+            const int l = peel_owner_panel(q, npl);
+            const int J = l * world + rank;
+            if (J * TW >= U) continue;
+            const int rowlimit = min((J + 1) * TW, U);
+            const int WL = (rowlimit + 31) >> 5;                       // mask words that can name a stored row
+            const uint32_t* pbase = bits + d_panel_words_before(l, world, rank) + lane;
+            uint32_t* cp = planes_in_smem ? cp_smem + slot * cp_stride : cplanes + (size_t)l * cp_stride;
+            const int pass_words = one_pass ? WL : PEEL_WARPS * 3 * 32;   // <= 3 groups = 3072 rows per warp
+
+            for (int w0 = 0; w0 < WL; w0 += pass_words) {
+                const int w1 = min(WL, w0 + pass_words);
+                int rp = 1;
+                {
+                    const int groups = (w1 - w0 + 31) >> 5;
+                    const int per = min(nf, ((groups + PEEL_WARPS - 1) / PEEL_WARPS) << 10);
+                    while ((1 << rp) <= per + 7) ++rp;
+                    rp = min(rp, PEEL_RP);
+                }
+                const int pm = min(rp + 4, PEEL_PM);
+                uint32_t ones = 0, twos = 0, fours = 0, up[PEEL_UP];
+#pragma unroll
+                for (int p = 0; p < PEEL_UP; ++p) up[p] = 0;
+                int pend = 0, issued = 0, consumed = 0;
+                const int gfirst = w0 + warp * 32;
+                uint32_t m_next = (gfirst + lane < w1) ? __ldcg(fm + gfirst + lane) : 0u;
+                for (int g0 = gfirst; g0 < w1; g0 += PEEL_WARPS * 32) {
+                    const uint32_t m = m_next;                          // mask words are fetched one group ahead
+                    const int gn = g0 + PEEL_WARPS * 32 + lane;
+                    m_next = (gn < w1) ? __ldcg(fm + gn) : 0u;
+                    uint32_t nzl = __ballot_sync(0xFFFFFFFFu, m != 0u);
+                    while (nzl) {
+                        const int src = __ffs(nzl) - 1;
+                        nzl &= nzl - 1;
+                        uint32_t mw = __shfl_sync(0xFFFFFFFFu, m, src);
+                        const int base = (g0 + src) << 5;
+                        while (mw) {
+                            const int b = __ffs(mw) - 1;
+                            mw &= mw - 1;
+                            cp_async4(ring + (((issued & (PEEL_DEPTH - 1)) * 8 + pend) << 5) + lane,
+                                      pbase + (size_t)(base + b) * PW);
+                            if (++pend == 8) {
+                                cp_async_commit();
+                                pend = 0;
+                                ++issued;
+                                if (issued - consumed == PEEL_DEPTH) {
+                                    cp_async_wait<PEEL_DEPTH - 1>();
+                                    uint32_t x[8];
+#pragma unroll
+                                    for (int r = 0; r < 8; ++r)
+                                        x[r] = ring[(((consumed & (PEEL_DEPTH - 1)) * 8 + r) << 5) + lane];
+                                    csa8(ones, twos, fours, up, x);
+                                    ++consumed;
+                                }
+                            }
+                        }
+                    }
+                }
+                if (pend) {                                            // pad the last batch with zero rows
+                    for (int r = pend; r < 8; ++r) ring[(((issued & (PEEL_DEPTH - 1)) * 8 + r) << 5) + lane] = 0u;
+                    cp_async_commit();
+                    ++issued;
+                }
+                cp_async_wait<0>();
+                while (consumed < issued) {
+                    uint32_t x[8];
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) x[r] = ring[(((consumed & (PEEL_DEPTH - 1)) * 8 + r) << 5) + lane];
+                    csa8(ones, twos, fours, up, x);
+                    ++consumed;
+                }
+                // per-warp planes -> shared memory (only the planes that can be non-zero)
+                sh.merge[warp][0][lane] = ones;
+                sh.merge[warp][1][lane] = twos;
+                sh.merge[warp][2][lane] = fours;
+#pragma unroll
+                for (int p = 0; p < PEEL_UP; ++p)
+                    if (3 + p < pm) sh.merge[warp][3 + p][lane] = up[p];
+                for (int p = PEEL_RP; p < pm; ++p) sh.merge[warp][p][lane] = 0u;
+                __syncthreads();
+                for (int half = PEEL_WARPS / 2; half >= 1; half >>= 1) {
+                    if (warp < half) {
+                        uint32_t carry = 0;
+                        for (int p = 0; p < pm; ++p) {
+                            const uint32_t a = sh.merge[warp][p][lane], b = sh.merge[warp + half][p][lane];
+                            const uint32_t x = a ^ b;
+                            sh.merge[warp][p][lane] = x ^ carry;
+                            carry = (a & b) | (x & carry);
+                        }
+                    }
+                    __syncthreads();
+                }
                 if (warp == 0)
-                    peel_commit(cp, K, sh.merge[0], pm, lane, J, fl_next, &scal->nf3[(k + 1) % 3], sh.newmask);
+                    peel_commit_mask(cp, K, sh.merge[0], pm, lane, fm_next + (size_t)J * PW, w0 == 0,
+                                     &scal->nf3[(k + 1) % 3], sh.newmask);
                 __syncthreads();
                 for (int c = threadIdx.x; c < TW; c += blockDim.x)
                     if ((sh.newmask[c >> 5] >> (c & 31)) & 1u) rank_u[(size_t)l * TW + c] = k + 1;
@@ -1090,24 +1447,35 @@ static int apply(const Plan& P, int k, const uint32_t* masks, int* any_out, cuda
 }
 
 
-// Launch the persistent peel (single rank).  Returns EVX_OK and leaves the front count in scal->fronts.
-static int peel_persistent(const Plan& P, cudaStream_t s) {
+// The list-driven persistent kernel is the default; EVX_PEEL=masks selects the mask-driven variant
+// (same results; measured slower on B200: 3.4 vs 2.5 ms at N = 200k, see profiles/).
+static bool use_list_peel() {
+    const char* e = getenv("EVX_PEEL");
+    return !(e && strcmp(e, "masks") == 0);
+}
+
+// Launch the persistent peel.  peers == nullptr: single rank.  Otherwise the fused multi-rank kernel
+// (list-driven) with the peer buffers.  Leaves the front count in scal->fronts (-1 after a time-out).
+static int peel_persistent(const Plan& P, cudaStream_t s, const PeerTable* peers = nullptr) {
     const Layout& L = P.L;
+    const bool list = use_list_peel() || peers != nullptr;
     int dev = 0, sms = 0, per_sm = 0;
     EVX_CUDA(cudaGetDevice(&dev));
     EVX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     // Count planes go to shared memory when every CTA's share fits beside the merge buffer with two
     // CTAs per SM; otherwise they stay in the workspace (L2-resident, touched only by their owner).
-    const size_t base_smem = sizeof(PeelShared);
+    const size_t base_smem = list ? sizeof(PeelShared) : sizeof(PeelSharedM);
+    const void* kernel = !list ? (const void*)k_peel_masks
+                               : (peers ? (const void*)k_peel_persistent<true> : (const void*)k_peel_persistent<false>);
     const size_t cp_bytes = sizeof(uint32_t) * (size_t)(L.kplanes + 1) * PW;
     int target = sms * 2;
     if (target > L.npl) target = L.npl;
     if (target < 1) target = 1;
     const size_t slots = (size_t)ceil_div(L.npl, target);
-    int planes_in_smem = (base_smem + slots * cp_bytes <= 100 * 1024) ? 1 : 0;
+    int planes_in_smem = (base_smem + slots * cp_bytes <= 112 * 1024) ? 1 : 0;
     const size_t smem = base_smem + (planes_in_smem ? slots * cp_bytes : 0);
-    EVX_CUDA(cudaFuncSetAttribute(k_peel_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    EVX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_peel_persistent, PEEL_WARPS * 32, smem));
+    EVX_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    EVX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, PEEL_WARPS * 32, smem));
     EVX_REQUIRE(per_sm >= 1, EVX_ERR_CUDA, "persistent peel kernel does not fit on an SM");
     int grid = sms * per_sm;
     if (grid > target) grid = target;
@@ -1120,8 +1488,19 @@ static int peel_persistent(const Plan& P, cudaStream_t s) {
     Scal* scal = P.at<Scal>(L.scal);
     uint32_t* cpl = P.at<uint32_t>(L.cplanes);
     int npl = L.npl, K = L.kplanes, world = L.world, rank = L.rank;
-    void* args[] = {&bits, &count, &rank_u, &fa, &fb, &scal, &cpl, &npl, &K, &world, &rank, &planes_in_smem};
-    EVX_CUDA(cudaLaunchCooperativeKernel((void*)k_peel_persistent, dim3(grid), dim3(PEEL_WARPS * 32), args, smem, s));
+    if (list) {
+        PeerTable pt{};
+        if (peers) pt = *peers;
+        void* args[] = {&bits, &count, &rank_u, &fa, &fb, &scal, &cpl, &npl, &K, &world, &rank, &planes_in_smem, &pt};
+        EVX_CUDA(cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3(PEEL_WARPS * 32), args, smem, s));
+    } else {
+        uint32_t* fmask = P.at<uint32_t>(L.fmask);
+        int64_t mask_words = L.npad / 32;
+        EVX_CUDA(cudaMemsetAsync(fmask, 0, sizeof(uint32_t) * 2 * (size_t)mask_words, s));
+        void* args[] = {&bits, &count, &rank_u, &fmask, &mask_words, &scal, &cpl, &npl, &K, &world, &rank,
+                        &planes_in_smem};
+        EVX_CUDA(cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3(PEEL_WARPS * 32), args, smem, s));
+    }
     ++evx::launch_counter();
     return EVX_OK;
 }
@@ -1197,6 +1576,42 @@ extern "C" int evx_nds_shard_ranks(evx_nds_shard* p, int32_t* rank_partial, void
     k_write_ranks<<<(unsigned)ceil_div(L.n, 256), 256, 0, (cudaStream_t)stream>>>(
         p->P.at<int>(L.row2u), p->P.at<int>(L.rank_u), L.n, L.world, L.rank, rank_partial);
     EVX_LAUNCH_CHECK();
+    return EVX_OK;
+}
+
+extern "C" size_t evx_nds_shard_peer_bytes(const evx_nds_shard* p) {
+    if (!p) return 0;
+    return sizeof(PeerState) + 2 * sizeof(int) * (size_t)p->P.L.npad;
+}
+
+extern "C" int evx_nds_shard_peer_init(evx_nds_shard* p, void* local_peer_buf, void* stream) {
+    EVX_REQUIRE(p && local_peer_buf, EVX_ERR_ARG, "evx_nds_shard_peer_init: null argument");
+    EVX_CUDA(cudaMemsetAsync(local_peer_buf, 0, sizeof(PeerState), (cudaStream_t)stream));
+    return EVX_OK;
+}
+
+extern "C" int evx_nds_shard_peel_fused(evx_nds_shard* p, void* const* peer_bufs, int32_t* num_fronts, void* stream) {
+    EVX_REQUIRE(p && peer_bufs, EVX_ERR_ARG, "evx_nds_shard_peel_fused: null argument");
+    const Layout& L = p->P.L;
+    EVX_REQUIRE(L.world <= MAX_WORLD, EVX_ERR_ARG, "evx_nds_shard_peel_fused: world %d > %d", L.world, MAX_WORLD);
+    if (num_fronts) *num_fronts = 0;
+    if (L.n == 0) return EVX_OK;
+    PeerTable pt{};
+    for (int r = 0; r < L.world; ++r) {
+        EVX_REQUIRE(peer_bufs[r], EVX_ERR_ARG, "evx_nds_shard_peel_fused: peer buffer %d is null", r);
+        pt.base[r] = reinterpret_cast<char*>(peer_bufs[r]);
+    }
+    pt.world = L.world; pt.rank = L.rank; pt.npad = L.npad;
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = peel_persistent(p->P, s, &pt);
+    if (rc) return rc;
+    int fronts = 0;
+    Scal* scal = p->P.at<Scal>(L.scal);
+    EVX_CUDA(cudaMemcpyAsync(&fronts, &scal->fronts, sizeof(int), cudaMemcpyDeviceToHost, s));
+    EVX_CUDA(cudaStreamSynchronize(s));
+    EVX_REQUIRE(fronts >= 0, EVX_ERR_CUDA, "evx_nds_shard_peel_fused: a peer did not reach the barrier within 4 s");
+    if (num_fronts) *num_fronts = fronts;
+    g_last_fronts = fronts;
     return EVX_OK;
 }
 

@@ -103,6 +103,48 @@ class ShardedNonDominatedSort:
         return self.out
 
 
+class FusedShardedNonDominatedSort:
+    """Same result as ShardedNonDominatedSort, but the whole peel is ONE persistent kernel per rank:
+    front members travel between GPUs as peer stores over NVLink inside the kernel, and the per-front
+    barrier spans all ranks' CTAs - no NCCL call and no kernel launch per front.  Needs peer-mapped
+    memory, obtained from torch symmetric memory (plumbing only)."""
+
+    def __init__(self, n, m, group=None):
+        import ctypes
+
+        import torch.distributed._symmetric_memory as symm
+        if not dist.is_initialized():
+            raise EvoxMoError("FusedShardedNonDominatedSort needs an initialised process group")
+        self.group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
+        self.n, self.m = n, m
+        self.shard = _CudaShard(n, m, self.world, self.rank)
+        L = lib()
+        nbytes = int(L.evx_nds_shard_peer_bytes(self.shard.plan))
+        self.peer = symm.empty(nbytes, dtype=torch.uint8, device=self.shard.device)
+        self.handle = symm.rendezvous(self.peer, self.group.group_name)
+        ptrs = list(self.handle.buffer_ptrs)
+        self._ptrs = (ctypes.c_void_p * self.world)(*ptrs)
+        self._nf = ctypes.c_int32(0)
+        self.out = torch.zeros(n, dtype=torch.int32, device=self.shard.device)
+        self.num_fronts = 0
+
+    def __call__(self, x):
+        import ctypes
+        if self.n == 0:
+            return self.out
+        L = lib()
+        self.shard.build(x)
+        check(L.evx_nds_shard_peer_init(self.shard.plan, self.peer.data_ptr(), stream_ptr()))
+        torch.cuda.current_stream().synchronize()
+        dist.barrier(group=self.group)                 # every rank's peer state is clean before anyone writes to it
+        check(L.evx_nds_shard_peel_fused(self.shard.plan, self._ptrs, ctypes.byref(self._nf), stream_ptr()))
+        self.num_fronts = int(self._nf.value)
+        self.shard.ranks(self.out)
+        dist.all_reduce(self.out, op=dist.ReduceOp.SUM, group=self.group)
+        return self.out
+
+
 def sharded_evaluate(problem, state, X_local, group=None):
     """Evaluate this rank's slice of the population and all-gather the fitness, as
     std_workflow.py:187-200 + core/distributed.py:49-56 do."""

@@ -146,6 +146,16 @@ int evx_nds_shard_detect(evx_nds_shard* p, int32_t k, uint32_t* local_mask, void
  * counts; `any_out` (device int32) is set non-zero if the front was non-empty; asynchronous       */
 int evx_nds_shard_apply(evx_nds_shard* p, int32_t k, const uint32_t* all_masks, int32_t* any_out,
                         void* stream);
+/* Fused alternative to the detect / all-gather / apply loop: ONE persistent kernel per rank peels
+ * every front; new front members are written straight into every rank's list over NVLink (peer
+ * stores + system-scope atomics) and a barrier over all CTAs of all ranks separates the fronts.
+ * Each rank provides `peer_bytes` of peer-mapped memory (e.g. torch symmetric memory);
+ * peer_bufs[r] (HOST array of world device pointers) is rank r's buffer as mapped in this process.
+ * Sequence: build -> peer_init -> host-level barrier across ranks -> peel_fused (synchronises; fails
+ * with a message, never hangs, if a rank is more than 4 s late) -> ranks.  world <= 8.              */
+size_t evx_nds_shard_peer_bytes(const evx_nds_shard* p);
+int evx_nds_shard_peer_init(evx_nds_shard* p, void* local_peer_buf, void* stream);
+int evx_nds_shard_peel_fused(evx_nds_shard* p, void* const* peer_bufs, int32_t* num_fronts, void* stream);
 /* ranks of the columns this rank owns, scattered to original row order into rank_partial (device
  * int32 [n], zero elsewhere: a SUM all-reduce over ranks yields the final ranks); asynchronous    */
 int evx_nds_shard_ranks(evx_nds_shard* p, int32_t* rank_partial, void* stream);
