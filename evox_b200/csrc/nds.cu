@@ -48,13 +48,17 @@ struct Scal {
     unsigned int barrier;   // persistent peel: grid barrier arrivals (monotonic)
     unsigned int go;        // fused multi-rank peel: release word written by CTA 0
     int abort;              // fused multi-rank peel: a peer barrier timed out
+    int pub3[3];            // fused multi-rank peel: members this rank published, triple buffered
+    int xcnt[8];            // fused multi-rank peel: per-rank member counts of the current front
+    int xtotal;             // fused multi-rank peel: their sum (-1: time-out)
+    unsigned long long dbg[8];   // persistent peel: ns spent by CTA 0 / last CTA in accumulate, merge+commit, barrier
 };
 
 struct Layout {
     int64_t n, npad;
     int m, world, rank, np, npl, npl_max;
     size_t keys, idxA, idxB, skeyA, skeyB, flags, incl, cubtmp, cubtmp_bytes, ucols, row2u, count,
-        rank_u, flist, flist2, cplanes, mask, scal, bits, total, tcols, bkeyA, bkeyB, label, fmask;
+        rank_u, flist, flist2, cplanes, mask, scal, bits, total, tcols, bkeyA, bkeyB, label;
     int kplanes;
     int64_t bits_words;
 };
@@ -110,7 +114,6 @@ static Layout make_layout(int64_t n, int m, int world, int rank) {
     L.kplanes = 1;
     while ((1ll << L.kplanes) <= L.npad) ++L.kplanes;          // counts < npad fit in kplanes bits
     L.cplanes = take(sizeof(uint32_t) * (size_t)L.npl_max * (L.kplanes + 1) * PW);
-    L.fmask = take(sizeof(uint32_t) * 2 * (size_t)(L.npad / 32));   // front membership, double buffered
     L.mask = take(sizeof(uint32_t) * (size_t)L.npl_max * PW * world);
     L.scal = take(sizeof(Scal));
     L.bits_words = panel_words_before(L.npl, world, rank);
@@ -716,10 +719,12 @@ k_front_apply(const uint32_t* __restrict__ bits, int* __restrict__ count, const 
 // integers.  One grid-wide barrier per front.
 namespace cg = cooperative_groups;
 
-constexpr int PEEL_WARPS = 16;
+constexpr int PEEL_WARPS = 8;
+constexpr int PEEL_LOG_WARPS = 3;
+constexpr int PEEL_STAGES = 2;                      // gather-ring stages (32 row slots each) per warp
 constexpr int PEEL_UP = 9;                          // register planes 8 .. 2^11 (+ ones, twos, fours)
 constexpr int PEEL_RP = 3 + PEEL_UP;                // 12 planes per warp: up to 4095 rows per pass
-constexpr int PEEL_PM = PEEL_RP + 4;                // merged over 16 warps: 16 planes (16*4095 < 2^16)
+constexpr int PEEL_PM = PEEL_RP + PEEL_LOG_WARPS;   // merged over 8 warps: 15 planes (8*4095 < 2^15)
 constexpr int PEEL_ROWS_PER_WARP = (1 << PEEL_RP) - 32;
 constexpr int PEEL_ROWS_PER_PASS = PEEL_WARPS * PEEL_ROWS_PER_WARP;
 
@@ -732,34 +737,38 @@ __device__ __forceinline__ uint32_t ld_stream(const uint32_t* p) {
 __device__ __forceinline__ int peel_owner_panel(int q, int npl) { return npl - 1 - q; }   // heaviest first
 
 struct PeelShared {
-    uint32_t merge[PEEL_WARPS][PEEL_PM][32];
+    alignas(128) uint32_t merge[PEEL_WARPS][PEEL_PM][32];
+    alignas(128) uint32_t ring[PEEL_WARPS][PEEL_STAGES * 32][32];   // per-warp bulk-copy gather ring
+    alignas(8) uint64_t bars[PEEL_WARPS][PEEL_STAGES];
     uint32_t newmask[32];
     int nf;
+    int cnt[8];                 // fused multi-rank peel: members published by each rank for this front
 };
 
 // ---- peer-visible state of the fused multi-rank peel ------------------------------------------------
 // Every rank provides one buffer in peer-mapped memory (torch symmetric memory / CUDA IPC):
-// [PeerState | flistA npad ints | flistB npad ints].  Publishers write new front members straight
-// into EVERY rank's list over NVLink and bump every rank's counter with a system-scope atomic; the
-// per-front barrier spans all CTAs of all ranks (local arrive -> flags to peers -> local release).
+// [PeerState | list 0 | list 1], each list = world regions of `cap` ints, region r written only by
+// rank r.  A publisher reserves slots with a LOCAL atomic and writes the new front members straight
+// into its region on EVERY rank with posted stores over NVLink - no cross-GPU atomics.  The per-front
+// barrier spans all CTAs of all ranks: local arrive -> CTA 0 sends one 64-bit message (epoch, number
+// of members this rank published) to every rank -> waits for every rank's message -> local release.
 constexpr int MAX_WORLD = 8;
 struct PeerState {
-    int nf3[3];
+    unsigned long long xmsg[MAX_WORLD];     // (epoch << 32) | members published by rank r for the next front
     int abort;
-    unsigned int xflag[MAX_WORLD];
-    unsigned int pad[52];
+    unsigned int pad[47];
 };
 static_assert(sizeof(PeerState) == 256, "PeerState must stay 256 bytes");
 struct PeerTable {
     char* base[MAX_WORLD];
     int world, rank;
-    int64_t npad;
+    int64_t cap;                            // ints per region
 };
 __device__ __forceinline__ PeerState* peer_state(const PeerTable& pt, int r) {
     return reinterpret_cast<PeerState*>(pt.base[r]);
 }
-__device__ __forceinline__ int* peer_flist(const PeerTable& pt, int r, int which) {
-    return reinterpret_cast<int*>(pt.base[r] + sizeof(PeerState)) + (size_t)which * pt.npad;
+__device__ __forceinline__ int* peer_region(const PeerTable& pt, int on_rank, int which, int region) {
+    return reinterpret_cast<int*>(pt.base[on_rank] + sizeof(PeerState)) + ((size_t)which * pt.world + region) * pt.cap;
 }
 __device__ __forceinline__ unsigned long long global_ns() {
     unsigned long long t;
@@ -768,17 +777,18 @@ __device__ __forceinline__ unsigned long long global_ns() {
 }
 constexpr unsigned long long PEER_TIMEOUT_NS = 4000000000ull;      // a peer that is 4 s late is gone
 
-// Barrier over all CTAs of all ranks.  Returns the size of the next front, or -1 after a time-out
-// (every rank then leaves the kernel; nothing spins forever).
-__device__ __forceinline__ int world_barrier(Scal* scal, unsigned int& epoch, const PeerTable& pt, int nf_slot,
-                                             int* nf_smem) {
+// Barrier over all CTAs of all ranks.  Fills cnt_smem[r] with the number of members rank r published
+// for the coming front and returns their sum, or -1 after a time-out (every rank then leaves the
+// kernel; nothing spins forever).  `pub` is this rank's local publish counter for that front.
+__device__ __forceinline__ int world_barrier(Scal* scal, unsigned int& epoch, const PeerTable& pt, const int* pub,
+                                             int* cnt_smem, int* nf_smem) {
     __syncthreads();
     ++epoch;
     if (threadIdx.x == 0) {
         PeerState* me = peer_state(pt, pt.rank);
         const unsigned long long t0 = global_ns();
         bool dead = false;
-        __threadfence_system();
+        __threadfence_system();                                       // this CTA's peer stores are out
         atomicAdd(&scal->barrier, 1u);
         if (blockIdx.x == 0) {
             unsigned int v;
@@ -786,22 +796,33 @@ __device__ __forceinline__ int world_barrier(Scal* scal, unsigned int& epoch, co
                 asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&scal->barrier) : "memory");
             } while (v < epoch * gridDim.x);
             __threadfence_system();
-            for (int r = 0; r < pt.world; ++r)                        // tell every rank (and myself)
-                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(&peer_state(pt, r)->xflag[pt.rank]), "r"(epoch)
+            int mine;
+            asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(mine) : "l"(pub) : "memory");
+            const unsigned long long msg = ((unsigned long long)epoch << 32) | (unsigned int)mine;
+            for (int r = 0; r < pt.world; ++r)                        // one message to every rank (and myself)
+                asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(&peer_state(pt, r)->xmsg[pt.rank]), "l"(msg)
                              : "memory");
-            for (int r = 0; r < pt.world && !dead; ++r) {             // wait for every rank
+            int total = 0;
+            for (int r = 0; r < pt.world && !dead; ++r) {             // wait for every rank's message
+                unsigned long long m;
                 do {
-                    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(&me->xflag[r]) : "memory");
+                    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(m) : "l"(&me->xmsg[r]) : "memory");
+                    if ((unsigned int)(m >> 32) >= epoch) break;
                     int ab;
                     asm volatile("ld.relaxed.sys.global.s32 %0, [%1];" : "=r"(ab) : "l"(&me->abort) : "memory");
                     if (ab || global_ns() - t0 > PEER_TIMEOUT_NS) dead = true;
-                } while (v < epoch && !dead);
+                } while (!dead);
+                const int c = (int)(unsigned int)m;
+                scal->xcnt[r] = c;
+                total += c;
             }
+            __threadfence_system();                                   // acquire: peers' list stores are visible
             if (dead) {
                 for (int r = 0; r < pt.world; ++r)
                     asm volatile("st.relaxed.sys.global.s32 [%0], %1;" ::"l"(&peer_state(pt, r)->abort), "r"(1) : "memory");
-                scal->abort = 1;
+                total = -1;
             }
+            scal->xtotal = total;
             __threadfence();
             asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&scal->go), "r"(epoch) : "memory");
         } else {
@@ -811,19 +832,20 @@ __device__ __forceinline__ int world_barrier(Scal* scal, unsigned int& epoch, co
             } while (v < epoch && global_ns() - t0 < 2 * PEER_TIMEOUT_NS);
             if (v < epoch) dead = true;
         }
-        int ab;
-        asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(ab) : "l"(&scal->abort) : "memory");
-        int nf;
-        asm volatile("ld.relaxed.sys.global.s32 %0, [%1];" : "=r"(nf) : "l"(&me->nf3[nf_slot]) : "memory");
-        *nf_smem = (dead || ab) ? -1 : nf;
+        int total;
+        asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(total) : "l"(&scal->xtotal) : "memory");
+        for (int r = 0; r < pt.world; ++r)
+            asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(cnt_smem[r]) : "l"(&scal->xcnt[r]) : "memory");
+        *nf_smem = dead ? -1 : total;
     }
     __syncthreads();
     return *nf_smem;
 }
 
-// Warp 0, multi-rank: subtract, detect, retire, and append the new front members to every rank's list.
+// Warp 0, multi-rank: subtract, detect, retire, and write the new front members into this rank's
+// region of every rank's list.
 __device__ __forceinline__ void peel_commit_world(uint32_t* cp, int K, const uint32_t (*delta)[32], int pm, int lane,
-                                                  int J, const PeerTable& pt, int which_next, int nf_slot,
+                                                  int J, const PeerTable& pt, int which_next, int* pub,
                                                   uint32_t* newmask_out) {
     uint32_t borrow = 0, nz = 0;
     for (int p = 0; p < K; ++p) {
@@ -849,20 +871,20 @@ __device__ __forceinline__ void peel_commit_world(uint32_t* cp, int K, const uin
     }
     const int total = __shfl_sync(0xFFFFFFFFu, incl, 31);
     if (total == 0) return;                                           // warp-uniform
-    int mybase = 0;                                                   // lane r reserves the slots on rank r
-    if (lane < pt.world) mybase = atomicAdd_system(&peer_state(pt, lane)->nf3[nf_slot], total);
+    int base = 0;
+    if (lane == 0) base = atomicAdd(pub, total);                      // local slot reservation
+    base = __shfl_sync(0xFFFFFFFFu, base, 0) + incl - c;
     const int col0 = J * TW + lane * 32;
     for (int r = 0; r < pt.world; ++r) {
-        int base = __shfl_sync(0xFFFFFFFFu, mybase, r) + incl - c;
-        int* dst = peer_flist(pt, r, which_next);
+        int* dst = peer_region(pt, r, which_next, pt.rank) + base;
         uint32_t w = nw;
+        int o = 0;
         while (w) {
             const int b = __ffs(w) - 1;
             w &= w - 1;
-            dst[base++] = col0 + b;                                   // posted store over NVLink for r != rank
+            dst[o++] = col0 + b;                                      // posted store over NVLink for r != rank
         }
     }
-    __threadfence_system();
 }
 
 // Grid-wide barrier on a monotonically increasing counter (all CTAs are co-resident: cooperative
@@ -948,16 +970,105 @@ __device__ __forceinline__ void csa8(uint32_t& ones, uint32_t& twos, uint32_t& f
     }
 }
 
+// ---- bulk-copy gather ring -------------------------------------------------------------------------
+// A front row's 128-byte segment is fetched with cp.async.bulk (the TMA engine's 1-D copy): every
+// lane issues the copy of a DIFFERENT row, so one warp instruction starts up to 32 row fetches
+// (a per-lane load moves one row per warp instruction and made the gather LSU-issue bound).  Copies
+// complete on an mbarrier; each warp owns PEEL_STAGES stages of 32 row slots in shared memory and
+// consumes one stage while the next is in flight.
+struct Ring {
+    uint32_t* slots;             // [PEEL_STAGES][32 rows][32 words]
+    uint64_t* bars;              // [PEEL_STAGES] mbarriers
+    int issued = 0, consumed = 0;
+    int rows[PEEL_STAGES] = {0, 0};
+    uint32_t phase = 0;          // bit s: parity to wait for on stage s
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tWAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_copy_128(uint32_t* smem_dst, const uint32_t* gsrc, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 128, [%2];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+__device__ __forceinline__ void ring_consume(Ring& rg, int lane, uint32_t& ones, uint32_t& twos, uint32_t& fours,
+                                             uint32_t (&up)[PEEL_UP]);
+__device__ __forceinline__ void peel_accumulate_ring(const int* list, int cnt, int goff, int warp, int lane,
+                                                     int rowlimit, const uint32_t* panel, Ring& rg, uint32_t& ones,
+                                                     uint32_t& twos, uint32_t& fours, uint32_t (&up)[PEEL_UP]);
+
+__device__ __forceinline__ void ring_consume(Ring& rg, int lane, uint32_t& ones, uint32_t& twos, uint32_t& fours,
+                                             uint32_t (&up)[PEEL_UP]) {
+    const int st = rg.consumed & (PEEL_STAGES - 1);
+    mbar_wait(rg.bars + st, (rg.phase >> st) & 1u);
+    rg.phase ^= 1u << st;
+    const int n = rg.rows[st];
+    const uint32_t* base = rg.slots + (st << 10) + lane;
+    for (int r0 = 0; r0 < n; r0 += 8) {
+        uint32_t x[8];
+#pragma unroll
+        for (int r = 0; r < 8; ++r) x[r] = (r0 + r < n) ? base[(r0 + r) << 5] : 0u;
+        csa8(ones, twos, fours, up, x);
+    }
+    ++rg.consumed;
+}
+
+// Rows [0, cnt) of `list`: groups of 32 consecutive entries are dealt to the warps round-robin,
+// starting with warp `goff`.  Only entries that have storage in this panel (i < rowlimit) are fetched.
+// `panel` is the panel's base (row 0, word 0).
+__device__ __forceinline__ void peel_accumulate_ring(const int* list, int cnt, int goff, int warp, int lane,
+                                                     int rowlimit, const uint32_t* panel, Ring& rg, uint32_t& ones,
+                                                     uint32_t& twos, uint32_t& fours, uint32_t (&up)[PEEL_UP]) {
+    const int lo = ((warp - goff) & (PEEL_WARPS - 1)) * 32, step = PEEL_WARPS * 32;
+    int mine = (lo + lane < cnt) ? __ldcg(list + lo + lane) : 0x7FFFFFFF;
+    for (int t0 = lo; t0 < cnt; t0 += step) {
+        const int nxt = (t0 + step + lane < cnt) ? __ldcg(list + t0 + step + lane) : 0x7FFFFFFF;
+        const bool q = mine < rowlimit;
+        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, q);
+        if (bal) {
+            if (rg.issued - rg.consumed == PEEL_STAGES) ring_consume(rg, lane, ones, twos, fours, up);
+            const int st = rg.issued & (PEEL_STAGES - 1);
+            const int total = __popc(bal);
+            const int slot = __popc(bal & ((1u << lane) - 1u));
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // earlier reads of this stage are done
+            if (lane == 0) mbar_expect_tx(rg.bars + st, (uint32_t)total * 128u);
+            __syncwarp();
+            if (q) bulk_copy_128(rg.slots + (st << 10) + (slot << 5), panel + (size_t)mine * PW, rg.bars + st);
+            rg.rows[st] = total;
+            ++rg.issued;
+        }
+        mine = nxt;
+    }
+}
+
+// Consume everything still in flight.
+__device__ __forceinline__ void ring_drain(Ring& rg, int lane, uint32_t& ones, uint32_t& twos, uint32_t& fours,
+                                           uint32_t (&up)[PEEL_UP]) {
+    while (rg.consumed < rg.issued) ring_consume(rg, lane, ones, twos, fours, up);
+}
+
 template <bool MULTI>
 __global__ void __launch_bounds__(PEEL_WARPS * 32, 2)
 k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ count, int* __restrict__ rank_u,
                   int* flistA, int* flistB, Scal* scal, uint32_t* __restrict__ cplanes, int npl, int K, int world,
                   int rank, int planes_in_smem, PeerTable pt) {
-    if constexpr (MULTI) {                                            // lists and counters live in the peer buffer
-        flistA = peer_flist(pt, pt.rank, 0);
-        flistB = peer_flist(pt, pt.rank, 1);
-    }
-    int* const nf3 = MULTI ? peer_state(pt, pt.rank)->nf3 : scal->nf3;
+    int* const nf3 = scal->nf3;
     extern __shared__ __align__(16) unsigned char peel_smem_raw[];
     PeelShared& sh = *reinterpret_cast<PeelShared*>(peel_smem_raw);
     uint32_t* cp_smem = reinterpret_cast<uint32_t*>(peel_smem_raw + sizeof(PeelShared));
@@ -987,7 +1098,7 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
         }
         __syncthreads();
         if (warp == 0) {
-            if constexpr (MULTI) peel_commit_world(cp, K, nullptr, 0, lane, J, pt, 0, 0, sh.newmask);
+            if constexpr (MULTI) peel_commit_world(cp, K, nullptr, 0, lane, J, pt, 0, &scal->pub3[0], sh.newmask);
             else peel_commit(cp, K, nullptr, 0, lane, J, flistA, &nf3[0], sh.newmask);
         }
         __syncthreads();
@@ -995,13 +1106,26 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
             if ((sh.newmask[c >> 5] >> (c & 31)) & 1u) rank_u[(size_t)l * TW + c] = 0;
         __syncthreads();
     }
-    int nf = MULTI ? world_barrier(scal, epoch, pt, 0, &sh.nf) : grid_barrier(bar, epoch, &nf3[0], &sh.nf);
+    int nf = MULTI ? world_barrier(scal, epoch, pt, &scal->pub3[0], sh.cnt, &sh.nf)
+                   : grid_barrier(bar, epoch, &nf3[0], &sh.nf);
 
     // ---- fronts ----------------------------------------------------------------------------------
+    Ring rg;                                                          // this warp's gather ring, for the whole kernel
+    rg.slots = &sh.ring[warp][0][0];
+    rg.bars = &sh.bars[warp][0];
+    if (lane == 0) {
+        for (int st = 0; st < PEEL_STAGES; ++st) mbar_init(rg.bars + st, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
     int k = 0;
+    unsigned long long t_acc = 0, t_mc = 0, t_bar = 0, t_mark = global_ns();   // thread 0's phase clock
     for (;; ++k) {
         if (nf <= 0) break;
-        if (B == 0 && threadIdx.x == 0) nf3[(k + 2) % 3] = 0;
+        if (B == 0 && threadIdx.x == 0) {
+            if constexpr (MULTI) scal->pub3[(k + 2) % 3] = 0;
+            else nf3[(k + 2) % 3] = 0;
+        }
         const int* fl = (k & 1) ? flistB : flistA;
         int* fl_next = (k & 1) ? flistA : flistB;
         for (int q0 = 0, slot = 0; q0 < npl; q0 += G, ++slot) {
@@ -1011,39 +1135,40 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
             const int J = l * world + rank;
             if (J * TW >= U) continue;
             const int rowlimit = min((J + 1) * TW, U);
-            const uint32_t* pbase = bits + d_panel_words_before(l, world, rank) + lane;
+            const uint32_t* pbase = bits + d_panel_words_before(l, world, rank);
             uint32_t* cp = planes_in_smem ? cp_smem + slot * cp_stride : cplanes + (size_t)l * cp_stride;
 
-            for (int pass0 = 0; pass0 < nf; pass0 += PEEL_ROWS_PER_PASS) {
-                const int pass_n = min(nf - pass0, PEEL_ROWS_PER_PASS);
-                // groups of 32 consecutive list entries are dealt to the warps round-robin (the list
-                // is grouped by publishing panel, so contiguous slices would be badly unbalanced)
-                const int hi = pass0 + pass_n;
-                const int groups = (pass_n + 31) >> 5;
-                const int per = ((groups + PEEL_WARPS - 1) / PEEL_WARPS) << 5;   // rows a warp can see
-                int rp = 1;                                          // planes a warp can have touched
-                while ((1 << rp) <= per) ++rp;
-                rp = min(rp, PEEL_RP);
-                const int pm = min(rp + 4, PEEL_PM);
+            // A pass adds at most PEEL_ROWS_PER_PASS list entries (what 12 register planes per warp
+            // can hold), then merges and commits; almost always one pass per front.
+            int pr = 0, poff = 0;                                    // multi-rank: next region / offset
+            for (int pass0 = 0; pass0 < nf;) {
                 uint32_t ones = 0, twos = 0, fours = 0, up[PEEL_UP];
 #pragma unroll
                 for (int p = 0; p < PEEL_UP; ++p) up[p] = 0;
-                const int lo = pass0 + warp * 32, step = PEEL_WARPS * 32;
-                int mine = (lo + lane < hi) ? __ldcg(fl + lo + lane) : 0x7FFFFFFF;
-                for (int t0 = lo; t0 < hi; t0 += step) {
-                    const int nxt = (t0 + step + lane < hi) ? __ldcg(fl + t0 + step + lane) : 0x7FFFFFFF;
-                    uint32_t v[32];
-#pragma unroll
-                    for (int u = 0; u < 32; ++u) {
-                        const int i = __shfl_sync(0xFFFFFFFFu, mine, u);
-                        v[u] = (i < rowlimit) ? ld_stream(pbase + (size_t)i * PW) : 0u;
+                int pass_n = 0;
+                if constexpr (!MULTI) {
+                    pass_n = min(nf - pass0, PEEL_ROWS_PER_PASS);
+                    peel_accumulate_ring(fl + pass0, pass_n, 0, warp, lane, rowlimit, pbase, rg, ones, twos, fours, up);
+                } else {
+                    int budget = PEEL_ROWS_PER_PASS - 32 * MAX_WORLD, goff = 0;
+                    while (pr < pt.world && budget > 0) {
+                        const int avail = sh.cnt[pr] - poff;
+                        if (avail <= 0) { ++pr; poff = 0; continue; }
+                        const int take = min(avail, budget);
+                        peel_accumulate_ring(peer_region(pt, pt.rank, k & 1, pr) + poff, take, goff, warp, lane, rowlimit,
+                                             pbase, rg, ones, twos, fours, up);
+                        goff = (goff + ((take + 31) >> 5)) & (PEEL_WARPS - 1);
+                        budget -= take; pass_n += take; poff += take;
                     }
-                    csa8(ones, twos, fours, up, v);
-                    csa8(ones, twos, fours, up, v + 8);
-                    csa8(ones, twos, fours, up, v + 16);
-                    csa8(ones, twos, fours, up, v + 24);
-                    mine = nxt;
                 }
+                ring_drain(rg, lane, ones, twos, fours, up);
+                pass0 += pass_n;
+                const int groups = ((pass_n + 31) >> 5) + (MULTI ? MAX_WORLD : 0);
+                const int per = ((groups + PEEL_WARPS - 1) / PEEL_WARPS) << 5;   // rows a warp can have seen
+                int rp = 1;                                          // planes a warp can have touched
+                while ((1 << rp) <= per) ++rp;
+                rp = min(rp, PEEL_RP);
+                const int pm = min(rp + PEEL_LOG_WARPS, PEEL_PM);
                 // per-warp planes -> shared memory (only the planes that can be non-zero)
                 sh.merge[warp][0][lane] = ones;
                 sh.merge[warp][1][lane] = twos;
@@ -1053,6 +1178,7 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
                     if (3 + p < pm) sh.merge[warp][3 + p][lane] = up[p];
                 for (int p = PEEL_RP; p < pm; ++p) sh.merge[warp][p][lane] = 0u;
                 __syncthreads();
+                if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_acc += t - t_mark; t_mark = t; }
                 // bit-sliced tree merge: warp w += warp w + half
                 for (int half = PEEL_WARPS / 2; half >= 1; half >>= 1) {
                     if (warp < half) {
@@ -1068,7 +1194,8 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
                 }
                 if (warp == 0) {
                     if constexpr (MULTI)
-                        peel_commit_world(cp, K, sh.merge[0], pm, lane, J, pt, (k + 1) & 1, (k + 1) % 3, sh.newmask);
+                        peel_commit_world(cp, K, sh.merge[0], pm, lane, J, pt, (k + 1) & 1, &scal->pub3[(k + 1) % 3],
+                                          sh.newmask);
                     else
                         peel_commit(cp, K, sh.merge[0], pm, lane, J, fl_next, &nf3[(k + 1) % 3], sh.newmask);
                 }
@@ -1076,224 +1203,18 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
                 for (int c = threadIdx.x; c < TW; c += blockDim.x)
                     if ((sh.newmask[c >> 5] >> (c & 31)) & 1u) rank_u[(size_t)l * TW + c] = k + 1;
                 __syncthreads();
+                if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_mc += t - t_mark; t_mark = t; }
             }
         }
-        nf = MULTI ? world_barrier(scal, epoch, pt, (k + 1) % 3, &sh.nf)
+        nf = MULTI ? world_barrier(scal, epoch, pt, &scal->pub3[(k + 1) % 3], sh.cnt, &sh.nf)
                    : grid_barrier(bar, epoch, &nf3[(k + 1) % 3], &sh.nf);
+        if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_bar += t - t_mark; t_mark = t; }
     }
     if (B == 0 && threadIdx.x == 0) scal->fronts = (nf < 0) ? -1 : k;
-}
-
-// ------------------------------------------------------------------------------------------------
-// stage 3c: persistent peel driven by front MASKS (default single-rank path)
-// ------------------------------------------------------------------------------------------------
-// Same ownership, bit-sliced counts and merge as k_peel_persistent, but a front is published as its
-// membership bit mask (one 128-byte store per panel, no list, no slot atomics), and a panel's owner
-// scans only the mask words below its row limit, so rows that have no storage in the panel are never
-// visited.  Row segments are gathered with cp.async into a per-warp ring in shared memory (4 batches
-// of 8 rows in flight per warp, independent of registers) and consumed by the carry-save adders one
-// batch behind.
-constexpr int PEEL_DEPTH = 4;
-
-struct PeelSharedM {
-    uint32_t merge[PEEL_WARPS][PEEL_PM][32];
-    uint32_t ring[PEEL_WARPS][PEEL_DEPTH * 8][32];
-    uint32_t newmask[32];
-    int nf;
-};
-
-__device__ __forceinline__ void cp_async4(uint32_t* smem_dst, const uint32_t* gsrc) {
-    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gsrc) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
-// Warp 0: subtract, detect, retire, publish the panel's 32 mask words for the next front.
-__device__ __forceinline__ void peel_commit_mask(uint32_t* cp, int K, const uint32_t (*delta)[32], int pm, int lane,
-                                                 uint32_t* fmask_next_panel, bool first_pass, int* nf_next,
-                                                 uint32_t* newmask_out) {
-    uint32_t borrow = 0, nz = 0;
-    for (int p = 0; p < K; ++p) {
-        const uint32_t c = cp[p * PW + lane];
-        const uint32_t d = (p < pm) ? delta[p][lane] : 0u;
-        const uint32_t x = c ^ d;
-        const uint32_t r = x ^ borrow;
-        borrow = (~c & d) | (~x & borrow);
-        if (pm > 0) cp[p * PW + lane] = r;
-        nz |= r;
+    if (threadIdx.x == 0 && (B == 0 || B == G - 1)) {                 // CTA 0 owns the heaviest panels
+        unsigned long long* d = scal->dbg + (B == 0 ? 0 : 4);
+        d[0] = t_acc; d[1] = t_mc; d[2] = t_bar; d[3] = (unsigned long long)k;
     }
-    uint32_t alive = cp[K * PW + lane];
-    const uint32_t nw = alive & ~nz;
-    alive &= ~nw;
-    cp[K * PW + lane] = alive;
-    newmask_out[lane] = nw;
-    // one coalesced 128-byte store; later passes of the same front add to what the first one wrote
-    fmask_next_panel[lane] = first_pass ? nw : (fmask_next_panel[lane] | nw);
-    int total = __popc(nw);
-#pragma unroll
-    for (int o = 16; o >= 1; o >>= 1) total += __shfl_xor_sync(0xFFFFFFFFu, total, o);
-    if (lane == 0 && total) atomicAdd(nf_next, total);              // result unused: a fire-and-forget RED
-}
-
-__global__ void __launch_bounds__(PEEL_WARPS * 32, 2)
-k_peel_masks(const uint32_t* __restrict__ bits, const int* __restrict__ count, int* __restrict__ rank_u,
-             uint32_t* fmask, int64_t mask_words, Scal* scal, uint32_t* __restrict__ cplanes, int npl, int K, int world,
-             int rank, int planes_in_smem) {
-    extern __shared__ __align__(16) unsigned char peel_smem_raw[];
-    PeelSharedM& sh = *reinterpret_cast<PeelSharedM*>(peel_smem_raw);
-    uint32_t* cp_smem = reinterpret_cast<uint32_t*>(peel_smem_raw + sizeof(PeelSharedM));
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int G = gridDim.x, B = blockIdx.x;
-    const int U = scal->U;
-    const size_t cp_stride = (size_t)(K + 1) * PW;
-    unsigned int epoch = 0;
-    unsigned int* bar = reinterpret_cast<unsigned int*>(&scal->barrier);
-
-    // ---- init: int counts -> planes, alive mask, front 0 -----------------------------------------
-    for (int q0 = 0, slot = 0; q0 < npl; q0 += G, ++slot) {
-        const int q = q0 + ((slot & 1) ? (G - 1 - B) : B);
-        if (q >= npl) continue;                                     // CTA-uniform
-        const int l = peel_owner_panel(q, npl);
-        const int J = l * world + rank;
-        uint32_t* cp = planes_in_smem ? cp_smem + slot * cp_stride : cplanes + (size_t)l * cp_stride;
-        for (int c = threadIdx.x; c < TW; c += blockDim.x) {
-            const int j = J * TW + c;
-            const int v = (j < U) ? count[(size_t)l * TW + c] : 0;
-            for (int p = 0; p < K; ++p) {
-                const uint32_t w = __ballot_sync(0xFFFFFFFFu, (v >> p) & 1);
-                if (lane == 0) cp[p * PW + (c >> 5)] = w;
-            }
-            const uint32_t a = __ballot_sync(0xFFFFFFFFu, j < U);
-            if (lane == 0) cp[K * PW + (c >> 5)] = a;
-        }
-        __syncthreads();
-        if (warp == 0)
-            peel_commit_mask(cp, K, nullptr, 0, lane, fmask + (size_t)J * PW, true, &scal->nf3[0], sh.newmask);
-        __syncthreads();
-        for (int c = threadIdx.x; c < TW; c += blockDim.x)
-            if ((sh.newmask[c >> 5] >> (c & 31)) & 1u) rank_u[(size_t)l * TW + c] = 0;
-        __syncthreads();
-    }
-    int nf = grid_barrier(bar, epoch, &scal->nf3[0], &sh.nf);
-
-    // ---- fronts ----------------------------------------------------------------------------------
-    int k = 0;
-    uint32_t* ring = &sh.ring[warp][0][0];
-    for (;; ++k) {
-        if (nf == 0) break;
-        if (B == 0 && threadIdx.x == 0) scal->nf3[(k + 2) % 3] = 0;
-        const uint32_t* fm = fmask + (size_t)(k & 1) * mask_words;
-        uint32_t* fm_next = fmask + (size_t)((k + 1) & 1) * mask_words;
-        // a warp sees at most min(nf, rows it scans) rows per pass: keep that below the 12 planes
-        const bool one_pass = nf <= PEEL_ROWS_PER_WARP;
-        for (int q0 = 0, slot = 0; q0 < npl; q0 += G, ++slot) {
-            const int q = q0 + ((slot & 1) ? (G - 1 - B) : B);
-            if (q >= npl) continue;
-            const int l = peel_owner_panel(q, npl);
-            const int J = l * world + rank;
-            if (J * TW >= U) continue;
-            const int rowlimit = min((J + 1) * TW, U);
-            const int WL = (rowlimit + 31) >> 5;                       // mask words that can name a stored row
-            const uint32_t* pbase = bits + d_panel_words_before(l, world, rank) + lane;
-            uint32_t* cp = planes_in_smem ? cp_smem + slot * cp_stride : cplanes + (size_t)l * cp_stride;
-            const int pass_words = one_pass ? WL : PEEL_WARPS * 3 * 32;   // <= 3 groups = 3072 rows per warp
-
-            for (int w0 = 0; w0 < WL; w0 += pass_words) {
-                const int w1 = min(WL, w0 + pass_words);
-                int rp = 1;
-                {
-                    const int groups = (w1 - w0 + 31) >> 5;
-                    const int per = min(nf, ((groups + PEEL_WARPS - 1) / PEEL_WARPS) << 10);
-                    while ((1 << rp) <= per + 7) ++rp;
-                    rp = min(rp, PEEL_RP);
-                }
-                const int pm = min(rp + 4, PEEL_PM);
-                uint32_t ones = 0, twos = 0, fours = 0, up[PEEL_UP];
-#pragma unroll
-                for (int p = 0; p < PEEL_UP; ++p) up[p] = 0;
-                int pend = 0, issued = 0, consumed = 0;
-                const int gfirst = w0 + warp * 32;
-                uint32_t m_next = (gfirst + lane < w1) ? __ldcg(fm + gfirst + lane) : 0u;
-                for (int g0 = gfirst; g0 < w1; g0 += PEEL_WARPS * 32) {
-                    const uint32_t m = m_next;                          // mask words are fetched one group ahead
-                    const int gn = g0 + PEEL_WARPS * 32 + lane;
-                    m_next = (gn < w1) ? __ldcg(fm + gn) : 0u;
-                    uint32_t nzl = __ballot_sync(0xFFFFFFFFu, m != 0u);
-                    while (nzl) {
-                        const int src = __ffs(nzl) - 1;
-                        nzl &= nzl - 1;
-                        uint32_t mw = __shfl_sync(0xFFFFFFFFu, m, src);
-                        const int base = (g0 + src) << 5;
-                        while (mw) {
-                            const int b = __ffs(mw) - 1;
-                            mw &= mw - 1;
-                            cp_async4(ring + (((issued & (PEEL_DEPTH - 1)) * 8 + pend) << 5) + lane,
-                                      pbase + (size_t)(base + b) * PW);
-                            if (++pend == 8) {
-                                cp_async_commit();
-                                pend = 0;
-                                ++issued;
-                                if (issued - consumed == PEEL_DEPTH) {
-                                    cp_async_wait<PEEL_DEPTH - 1>();
-                                    uint32_t x[8];
-#pragma unroll
-                                    for (int r = 0; r < 8; ++r)
-                                        x[r] = ring[(((consumed & (PEEL_DEPTH - 1)) * 8 + r) << 5) + lane];
-                                    csa8(ones, twos, fours, up, x);
-                                    ++consumed;
-                                }
-                            }
-                        }
-                    }
-                }
-                if (pend) {                                            // pad the last batch with zero rows
-                    for (int r = pend; r < 8; ++r) ring[(((issued & (PEEL_DEPTH - 1)) * 8 + r) << 5) + lane] = 0u;
-                    cp_async_commit();
-                    ++issued;
-                }
-                cp_async_wait<0>();
-                while (consumed < issued) {
-                    uint32_t x[8];
-#pragma unroll
-                    for (int r = 0; r < 8; ++r) x[r] = ring[(((consumed & (PEEL_DEPTH - 1)) * 8 + r) << 5) + lane];
-                    csa8(ones, twos, fours, up, x);
-                    ++consumed;
-                }
-                // per-warp planes -> shared memory (only the planes that can be non-zero)
-                sh.merge[warp][0][lane] = ones;
-                sh.merge[warp][1][lane] = twos;
-                sh.merge[warp][2][lane] = fours;
-#pragma unroll
-                for (int p = 0; p < PEEL_UP; ++p)
-                    if (3 + p < pm) sh.merge[warp][3 + p][lane] = up[p];
-                for (int p = PEEL_RP; p < pm; ++p) sh.merge[warp][p][lane] = 0u;
-                __syncthreads();
-                for (int half = PEEL_WARPS / 2; half >= 1; half >>= 1) {
-                    if (warp < half) {
-                        uint32_t carry = 0;
-                        for (int p = 0; p < pm; ++p) {
-                            const uint32_t a = sh.merge[warp][p][lane], b = sh.merge[warp + half][p][lane];
-                            const uint32_t x = a ^ b;
-                            sh.merge[warp][p][lane] = x ^ carry;
-                            carry = (a & b) | (x & carry);
-                        }
-                    }
-                    __syncthreads();
-                }
-                if (warp == 0)
-                    peel_commit_mask(cp, K, sh.merge[0], pm, lane, fm_next + (size_t)J * PW, w0 == 0,
-                                     &scal->nf3[(k + 1) % 3], sh.newmask);
-                __syncthreads();
-                for (int c = threadIdx.x; c < TW; c += blockDim.x)
-                    if ((sh.newmask[c >> 5] >> (c & 31)) & 1u) rank_u[(size_t)l * TW + c] = k + 1;
-                __syncthreads();
-            }
-        }
-        nf = grid_barrier(bar, epoch, &scal->nf3[(k + 1) % 3], &sh.nf);
-    }
-    if (B == 0 && threadIdx.x == 0) scal->fronts = k;
 }
 
 __global__ void k_write_ranks(const int* __restrict__ row2u, const int* __restrict__ rank_u, int64_t n, int world,
@@ -1447,26 +1368,18 @@ static int apply(const Plan& P, int k, const uint32_t* masks, int* any_out, cuda
 }
 
 
-// The list-driven persistent kernel is the default; EVX_PEEL=masks selects the mask-driven variant
-// (same results; measured slower on B200: 3.4 vs 2.5 ms at N = 200k, see profiles/).
-static bool use_list_peel() {
-    const char* e = getenv("EVX_PEEL");
-    return !(e && strcmp(e, "masks") == 0);
-}
-
 // Launch the persistent peel.  peers == nullptr: single rank.  Otherwise the fused multi-rank kernel
 // (list-driven) with the peer buffers.  Leaves the front count in scal->fronts (-1 after a time-out).
 static int peel_persistent(const Plan& P, cudaStream_t s, const PeerTable* peers = nullptr) {
     const Layout& L = P.L;
-    const bool list = use_list_peel() || peers != nullptr;
+
     int dev = 0, sms = 0, per_sm = 0;
     EVX_CUDA(cudaGetDevice(&dev));
     EVX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     // Count planes go to shared memory when every CTA's share fits beside the merge buffer with two
     // CTAs per SM; otherwise they stay in the workspace (L2-resident, touched only by their owner).
-    const size_t base_smem = list ? sizeof(PeelShared) : sizeof(PeelSharedM);
-    const void* kernel = !list ? (const void*)k_peel_masks
-                               : (peers ? (const void*)k_peel_persistent<true> : (const void*)k_peel_persistent<false>);
+    const size_t base_smem = sizeof(PeelShared);
+    const void* kernel = peers ? (const void*)k_peel_persistent<true> : (const void*)k_peel_persistent<false>;
     const size_t cp_bytes = sizeof(uint32_t) * (size_t)(L.kplanes + 1) * PW;
     int target = sms * 2;
     if (target > L.npl) target = L.npl;
@@ -1488,19 +1401,10 @@ static int peel_persistent(const Plan& P, cudaStream_t s, const PeerTable* peers
     Scal* scal = P.at<Scal>(L.scal);
     uint32_t* cpl = P.at<uint32_t>(L.cplanes);
     int npl = L.npl, K = L.kplanes, world = L.world, rank = L.rank;
-    if (list) {
-        PeerTable pt{};
-        if (peers) pt = *peers;
-        void* args[] = {&bits, &count, &rank_u, &fa, &fb, &scal, &cpl, &npl, &K, &world, &rank, &planes_in_smem, &pt};
-        EVX_CUDA(cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3(PEEL_WARPS * 32), args, smem, s));
-    } else {
-        uint32_t* fmask = P.at<uint32_t>(L.fmask);
-        int64_t mask_words = L.npad / 32;
-        EVX_CUDA(cudaMemsetAsync(fmask, 0, sizeof(uint32_t) * 2 * (size_t)mask_words, s));
-        void* args[] = {&bits, &count, &rank_u, &fmask, &mask_words, &scal, &cpl, &npl, &K, &world, &rank,
-                        &planes_in_smem};
-        EVX_CUDA(cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3(PEEL_WARPS * 32), args, smem, s));
-    }
+    PeerTable pt{};
+    if (peers) pt = *peers;
+    void* args[] = {&bits, &count, &rank_u, &fa, &fb, &scal, &cpl, &npl, &K, &world, &rank, &planes_in_smem, &pt};
+    EVX_CUDA(cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3(PEEL_WARPS * 32), args, smem, s));
     ++evx::launch_counter();
     return EVX_OK;
 }
@@ -1581,7 +1485,8 @@ extern "C" int evx_nds_shard_ranks(evx_nds_shard* p, int32_t* rank_partial, void
 
 extern "C" size_t evx_nds_shard_peer_bytes(const evx_nds_shard* p) {
     if (!p) return 0;
-    return sizeof(PeerState) + 2 * sizeof(int) * (size_t)p->P.L.npad;
+    const Layout& L = p->P.L;
+    return sizeof(PeerState) + 2 * sizeof(int) * (size_t)L.world * ((size_t)L.npl_max * TW);
 }
 
 extern "C" int evx_nds_shard_peer_init(evx_nds_shard* p, void* local_peer_buf, void* stream) {
@@ -1601,7 +1506,7 @@ extern "C" int evx_nds_shard_peel_fused(evx_nds_shard* p, void* const* peer_bufs
         EVX_REQUIRE(peer_bufs[r], EVX_ERR_ARG, "evx_nds_shard_peel_fused: peer buffer %d is null", r);
         pt.base[r] = reinterpret_cast<char*>(peer_bufs[r]);
     }
-    pt.world = L.world; pt.rank = L.rank; pt.npad = L.npad;
+    pt.world = L.world; pt.rank = L.rank; pt.cap = (int64_t)L.npl_max * TW;
     cudaStream_t s = (cudaStream_t)stream;
     int rc = peel_persistent(p->P, s, &pt);
     if (rc) return rc;
@@ -1612,6 +1517,13 @@ extern "C" int evx_nds_shard_peel_fused(evx_nds_shard* p, void* const* peer_bufs
     EVX_REQUIRE(fronts >= 0, EVX_ERR_CUDA, "evx_nds_shard_peel_fused: a peer did not reach the barrier within 4 s");
     if (num_fronts) *num_fronts = fronts;
     g_last_fronts = fronts;
+    return EVX_OK;
+}
+
+extern "C" int evx_debug_peel_times(evx_nds_shard* p, uint64_t* out8) {
+    EVX_REQUIRE(p && out8, EVX_ERR_ARG, "evx_debug_peel_times: null argument");
+    Scal* scal = p->P.at<Scal>(p->P.L.scal);
+    EVX_CUDA(cudaMemcpy(out8, scal->dbg, sizeof(uint64_t) * 8, cudaMemcpyDeviceToHost));
     return EVX_OK;
 }
 
