@@ -24,6 +24,7 @@
 
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "common.cuh"
 
@@ -36,6 +37,8 @@ constexpr int TILE_WARPS = 4;
 constexpr int SLAB = 32 * RB;       // rows per warp and pass
 constexpr int MAX_SLABS = 4;        // passes per warp (count planes stay in registers across passes)
 constexpr int APPLY_WARPS = 8;
+constexpr int PEEL_MAX_GRID = 1024;  // upper bound on the CTAs of the persistent peel kernel
+constexpr int PEEL_PM_MAX = 16;      // >= merged count planes of the persistent peel (PEEL_PM)
 constexpr int ANY_SLOTS = 64;
 
 struct Scal {
@@ -58,7 +61,7 @@ struct Layout {
     int64_t n, npad;
     int m, world, rank, np, npl, npl_max;
     size_t keys, idxA, idxB, skeyA, skeyB, flags, incl, cubtmp, cubtmp_bytes, ucols, row2u, count,
-        rank_u, flist, flist2, cplanes, mask, scal, bits, total, tcols, bkeyA, bkeyB, label;
+        rank_u, flist, flist2, cplanes, mask, scal, bits, total, tcols, bkeyA, bkeyB, label, items, partials, pdone;
     int kplanes;
     int64_t bits_words;
 };
@@ -115,6 +118,9 @@ static Layout make_layout(int64_t n, int m, int world, int rank) {
     while ((1ll << L.kplanes) <= L.npad) ++L.kplanes;          // counts < npad fit in kplanes bits
     L.cplanes = take(sizeof(uint32_t) * (size_t)L.npl_max * (L.kplanes + 1) * PW);
     L.mask = take(sizeof(uint32_t) * (size_t)L.npl_max * PW * world);
+    L.items = take(sizeof(int) * 4 * (size_t)(L.npl_max + 2 * PEEL_MAX_GRID));
+    L.partials = take(sizeof(uint32_t) * (size_t)PEEL_MAX_GRID * PEEL_PM_MAX * 32);
+    L.pdone = take(sizeof(unsigned int) * 2 * (size_t)L.npl_max);      // arrivals, commits
     L.scal = take(sizeof(Scal));
     L.bits_words = panel_words_before(L.npl, world, rank);
     L.bits = take(sizeof(uint32_t) * (size_t)L.bits_words);
@@ -725,6 +731,13 @@ constexpr int PEEL_STAGES = 2;                      // gather-ring stages (32 ro
 constexpr int PEEL_UP = 9;                          // register planes 8 .. 2^11 (+ ones, twos, fours)
 constexpr int PEEL_RP = 3 + PEEL_UP;                // 12 planes per warp: up to 4095 rows per pass
 constexpr int PEEL_PM = PEEL_RP + PEEL_LOG_WARPS;   // merged over 8 warps: 15 planes (8*4095 < 2^15)
+static_assert(PEEL_PM <= PEEL_PM_MAX, "raise PEEL_PM_MAX");
+constexpr int PEEL_MAX_STRIPES = 16;                // CTAs that may share one heavy panel
+
+// One unit of peel work: a panel, or one of `nstripes` row stripes of a heavy panel.
+struct PeelItem {
+    int l, stripe, nstripes, slot;
+};
 constexpr int PEEL_ROWS_PER_WARP = (1 << PEEL_RP) - 32;
 constexpr int PEEL_ROWS_PER_PASS = PEEL_WARPS * PEEL_ROWS_PER_WARP;
 
@@ -733,8 +746,6 @@ __device__ __forceinline__ uint32_t ld_stream(const uint32_t* p) {
     asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
     return v;
 }
-
-__device__ __forceinline__ int peel_owner_panel(int q, int npl) { return npl - 1 - q; }   // heaviest first
 
 struct PeelShared {
     alignas(128) uint32_t merge[PEEL_WARPS][PEEL_PM][32];
@@ -1009,7 +1020,7 @@ __device__ __forceinline__ void bulk_copy_128(uint32_t* smem_dst, const uint32_t
 
 __device__ __forceinline__ void ring_consume(Ring& rg, int lane, uint32_t& ones, uint32_t& twos, uint32_t& fours,
                                              uint32_t (&up)[PEEL_UP]);
-__device__ __forceinline__ void peel_accumulate_ring(const int* list, int cnt, int goff, int warp, int lane,
+__device__ __forceinline__ void peel_accumulate_ring(const int* list, int cnt, int goff, int wq, int totw, int lane,
                                                      int rowlimit, const uint32_t* panel, Ring& rg, uint32_t& ones,
                                                      uint32_t& twos, uint32_t& fours, uint32_t (&up)[PEEL_UP]);
 
@@ -1029,13 +1040,16 @@ __device__ __forceinline__ void ring_consume(Ring& rg, int lane, uint32_t& ones,
     ++rg.consumed;
 }
 
-// Rows [0, cnt) of `list`: groups of 32 consecutive entries are dealt to the warps round-robin,
-// starting with warp `goff`.  Only entries that have storage in this panel (i < rowlimit) are fetched.
-// `panel` is the panel's base (row 0, word 0).
-__device__ __forceinline__ void peel_accumulate_ring(const int* list, int cnt, int goff, int warp, int lane,
+// Rows [0, cnt) of `list`: groups of 32 consecutive entries are dealt round-robin to the `totw` warps
+// working on this panel (all stripes together; this warp is number `wq`), starting with warp `goff`.
+// Only entries that have storage in this panel (i < rowlimit) are fetched.  `panel` is the panel's
+// base (row 0, word 0).
+__device__ __forceinline__ void peel_accumulate_ring(const int* list, int cnt, int goff, int wq, int totw, int lane,
                                                      int rowlimit, const uint32_t* panel, Ring& rg, uint32_t& ones,
                                                      uint32_t& twos, uint32_t& fours, uint32_t (&up)[PEEL_UP]) {
-    const int lo = ((warp - goff) & (PEEL_WARPS - 1)) * 32, step = PEEL_WARPS * 32;
+    int first = wq - goff;
+    if (first < 0) first += totw;
+    const int lo = first * 32, step = totw * 32;
     int mine = (lo + lane < cnt) ? __ldcg(list + lo + lane) : 0x7FFFFFFF;
     for (int t0 = lo; t0 < cnt; t0 += step) {
         const int nxt = (t0 + step + lane < cnt) ? __ldcg(list + t0 + step + lane) : 0x7FFFFFFF;
@@ -1066,10 +1080,11 @@ __device__ __forceinline__ void ring_drain(Ring& rg, int lane, uint32_t& ones, u
 template <bool MULTI>
 __global__ void __launch_bounds__(PEEL_WARPS * 32, 2)
 k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ count, int* __restrict__ rank_u,
-                  int* flistA, int* flistB, Scal* scal, uint32_t* __restrict__ cplanes, int npl, int K, int world,
-                  int rank, int planes_in_smem, PeerTable pt) {
+                  int* flistA, int* flistB, Scal* scal, uint32_t* __restrict__ cplanes, const PeelItem* __restrict__ items,
+                  int slots, uint32_t* partials, unsigned int* pdone, unsigned int* pcommit, int K, int world, int rank,
+                  int planes_in_smem, PeerTable pt) {
     int* const nf3 = scal->nf3;
-    extern __shared__ __align__(16) unsigned char peel_smem_raw[];
+    extern __shared__ __align__(128) unsigned char peel_smem_raw[];
     PeelShared& sh = *reinterpret_cast<PeelShared*>(peel_smem_raw);
     uint32_t* cp_smem = reinterpret_cast<uint32_t*>(peel_smem_raw + sizeof(PeelShared));
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1079,13 +1094,13 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
     unsigned int epoch = 0;
     unsigned int* bar = reinterpret_cast<unsigned int*>(&scal->barrier);
 
-    // ---- init: int counts -> planes, alive mask, front 0 -----------------------------------------
-    for (int q0 = 0, slot = 0; q0 < npl; q0 += G, ++slot) {
-        const int q = q0 + ((slot & 1) ? (G - 1 - B) : B);
-        if (q >= npl) continue;                                     // CTA-uniform
-        const int l = peel_owner_panel(q, npl);
+    // ---- init: int counts -> planes, alive mask, front 0 (stripe 0 of every panel) ----------------
+    for (int sl = 0; sl < slots; ++sl) {
+        const PeelItem it = items[(size_t)sl * G + B];
+        if (it.l < 0 || it.stripe != 0) continue;                   // CTA-uniform
+        const int l = it.l;
         const int J = l * world + rank;
-        uint32_t* cp = planes_in_smem ? cp_smem + slot * cp_stride : cplanes + (size_t)l * cp_stride;
+        uint32_t* cp = planes_in_smem ? cp_smem + it.slot * cp_stride : cplanes + (size_t)l * cp_stride;
         for (int c = threadIdx.x; c < TW; c += blockDim.x) {        // 32 consecutive columns per warp step
             const int j = J * TW + c;
             const int v = (j < U) ? count[(size_t)l * TW + c] : 0;
@@ -1128,18 +1143,24 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
         }
         const int* fl = (k & 1) ? flistB : flistA;
         int* fl_next = (k & 1) ? flistA : flistB;
-        for (int q0 = 0, slot = 0; q0 < npl; q0 += G, ++slot) {
-            const int q = q0 + ((slot & 1) ? (G - 1 - B) : B);
-            if (q >= npl) continue;
-            const int l = peel_owner_panel(q, npl);
+        for (int sl = 0; sl < slots; ++sl) {
+            const PeelItem it = items[(size_t)sl * G + B];
+            if (it.l < 0) continue;                                   // CTA-uniform
+            const int l = it.l;
             const int J = l * world + rank;
             if (J * TW >= U) continue;
             const int rowlimit = min((J + 1) * TW, U);
             const uint32_t* pbase = bits + d_panel_words_before(l, world, rank);
-            uint32_t* cp = planes_in_smem ? cp_smem + slot * cp_stride : cplanes + (size_t)l * cp_stride;
+            uint32_t* cp = planes_in_smem ? cp_smem + it.slot * cp_stride : cplanes + (size_t)l * cp_stride;
+            // stripes actually used for this front: at least 512 list entries each (a short front is
+            // cheaper in one CTA than spread over many and merged)
+            const int ns = min(it.nstripes, max(1, nf >> 9));
+            if (it.stripe >= ns) continue;                            // CTA-uniform
+            const int totw = ns * PEEL_WARPS, wq = it.stripe * PEEL_WARPS + warp;
 
-            // A pass adds at most PEEL_ROWS_PER_PASS list entries (what 12 register planes per warp
-            // can hold), then merges and commits; almost always one pass per front.
+            // A pass adds at most `pass_cap` list entries (what 12 register planes per warp can hold),
+            // then merges and commits; almost always one pass per front.
+            const int pass_cap = ns * (PEEL_ROWS_PER_PASS - 32 * MAX_WORLD);
             int pr = 0, poff = 0;                                    // multi-rank: next region / offset
             for (int pass0 = 0; pass0 < nf;) {
                 uint32_t ones = 0, twos = 0, fours = 0, up[PEEL_UP];
@@ -1147,28 +1168,30 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
                 for (int p = 0; p < PEEL_UP; ++p) up[p] = 0;
                 int pass_n = 0;
                 if constexpr (!MULTI) {
-                    pass_n = min(nf - pass0, PEEL_ROWS_PER_PASS);
-                    peel_accumulate_ring(fl + pass0, pass_n, 0, warp, lane, rowlimit, pbase, rg, ones, twos, fours, up);
+                    pass_n = min(nf - pass0, pass_cap);
+                    peel_accumulate_ring(fl + pass0, pass_n, 0, wq, totw, lane, rowlimit, pbase, rg, ones, twos, fours, up);
                 } else {
-                    int budget = PEEL_ROWS_PER_PASS - 32 * MAX_WORLD, goff = 0;
+                    int budget = pass_cap, goff = 0;
                     while (pr < pt.world && budget > 0) {
                         const int avail = sh.cnt[pr] - poff;
                         if (avail <= 0) { ++pr; poff = 0; continue; }
                         const int take = min(avail, budget);
-                        peel_accumulate_ring(peer_region(pt, pt.rank, k & 1, pr) + poff, take, goff, warp, lane, rowlimit,
-                                             pbase, rg, ones, twos, fours, up);
-                        goff = (goff + ((take + 31) >> 5)) & (PEEL_WARPS - 1);
+                        peel_accumulate_ring(peer_region(pt, pt.rank, k & 1, pr) + poff, take, goff, wq, totw, lane,
+                                             rowlimit, pbase, rg, ones, twos, fours, up);
+                        goff = (goff + ((take + 31) >> 5)) % totw;
                         budget -= take; pass_n += take; poff += take;
                     }
                 }
                 ring_drain(rg, lane, ones, twos, fours, up);
                 pass0 += pass_n;
                 const int groups = ((pass_n + 31) >> 5) + (MULTI ? MAX_WORLD : 0);
-                const int per = ((groups + PEEL_WARPS - 1) / PEEL_WARPS) << 5;   // rows a warp can have seen
+                const int per = ((groups + totw - 1) / totw) << 5;    // rows a warp can have seen
                 int rp = 1;                                          // planes a warp can have touched
                 while ((1 << rp) <= per) ++rp;
                 rp = min(rp, PEEL_RP);
-                const int pm = min(rp + PEEL_LOG_WARPS, PEEL_PM);
+                const int pmw = min(rp + PEEL_LOG_WARPS, PEEL_PM);    // planes after the in-CTA merge
+                int pm = pmw;                                        // ... and after merging the stripes
+                if (ns > 1) { int e = 1; while ((1 << e) < ns) ++e; pm = min(pmw + e, PEEL_PM); }
                 // per-warp planes -> shared memory (only the planes that can be non-zero)
                 sh.merge[warp][0][lane] = ones;
                 sh.merge[warp][1][lane] = twos;
@@ -1192,17 +1215,68 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
                     }
                     __syncthreads();
                 }
-                if (warp == 0) {
-                    if constexpr (MULTI)
-                        peel_commit_world(cp, K, sh.merge[0], pm, lane, J, pt, (k + 1) & 1, &scal->pub3[(k + 1) % 3],
-                                          sh.newmask);
-                    else
-                        peel_commit(cp, K, sh.merge[0], pm, lane, J, fl_next, &nf3[(k + 1) % 3], sh.newmask);
+                bool commit = true;
+                unsigned int commits_before = 0;
+                if (ns > 1) {
+                    // Heavy panel shared by several CTAs: park this stripe's partial sum in global
+                    // memory; whichever stripe arrives last adds the others to its own and commits.
+                    uint32_t* mine = partials + ((size_t)B * PEEL_PM_MAX) * 32;
+                    if (warp == 0)
+                        for (int p = 0; p < pm; ++p) __stcg(mine + p * 32 + lane, sh.merge[0][p][lane]);
+                    __syncthreads();
+                    if (threadIdx.x == 0) {
+                        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(commits_before) : "l"(&pcommit[l]) : "memory");
+                        __threadfence();
+                        const unsigned int old = atomicAdd(&pdone[l], 1u);
+                        const bool last = old + 1u == (unsigned int)ns;
+                        if (last) pdone[l] = 0u;                      // nobody touches it again before the next pass
+                        sh.nf = last ? 1 : 0;
+                        __threadfence();
+                    }
+                    __syncthreads();
+                    commit = sh.nf != 0;
+                    if (commit && warp == 0) {
+                        for (int st2 = 0; st2 < ns; ++st2) {
+                            if (st2 == it.stripe) continue;
+                            const uint32_t* other = partials + ((size_t)(B - it.stripe + st2) * PEEL_PM_MAX) * 32;
+                            uint32_t carry = 0;
+                            for (int p = 0; p < pm; ++p) {
+                                const uint32_t a = sh.merge[0][p][lane], b2 = __ldcg(other + p * 32 + lane);
+                                const uint32_t x = a ^ b2;
+                                sh.merge[0][p][lane] = x ^ carry;
+                                carry = (a & b2) | (x & carry);
+                            }
+                        }
+                    }
+                    __syncthreads();
+                }
+                if (commit) {
+                    if (warp == 0) {
+                        if constexpr (MULTI)
+                            peel_commit_world(cp, K, sh.merge[0], pm, lane, J, pt, (k + 1) & 1, &scal->pub3[(k + 1) % 3],
+                                              sh.newmask);
+                        else
+                            peel_commit(cp, K, sh.merge[0], pm, lane, J, fl_next, &nf3[(k + 1) % 3], sh.newmask);
+                    }
+                    __syncthreads();
+                    for (int c = threadIdx.x; c < TW; c += blockDim.x)
+                        if ((sh.newmask[c >> 5] >> (c & 31)) & 1u) rank_u[(size_t)l * TW + c] = k + 1;
                 }
                 __syncthreads();
-                for (int c = threadIdx.x; c < TW; c += blockDim.x)
-                    if ((sh.newmask[c >> 5] >> (c & 31)) & 1u) rank_u[(size_t)l * TW + c] = k + 1;
-                __syncthreads();
+                if (ns > 1) {
+                    // A further pass of the same front may only start (and overwrite the parked
+                    // partial sums) once this pass has been committed.
+                    if (threadIdx.x == 0) {
+                        if (commit) { __threadfence(); atomicAdd(&pcommit[l], 1u); }
+                        if (pass0 < nf) {
+                            unsigned int v;
+                            do {
+                                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&pcommit[l]) : "memory");
+                            } while (v == commits_before);
+                        }
+                    }
+                    __syncthreads();
+                }
                 if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_mc += t - t_mark; t_mark = t; }
             }
         }
@@ -1369,30 +1443,86 @@ static int apply(const Plan& P, int k, const uint32_t* masks, int* any_out, cuda
 
 
 // Launch the persistent peel.  peers == nullptr: single rank.  Otherwise the fused multi-rank kernel
-// (list-driven) with the peer buffers.  Leaves the front count in scal->fronts (-1 after a time-out).
+// with the peer buffers.  Leaves the front count in scal->fronts (-1 after a time-out).
+//
+// Work assignment (host, per call): with at least as many panels as CTAs every panel is one item
+// and the items are dealt boustrophedon, heaviest first, so the triangular panel sizes balance.
+// With fewer panels than CTAs the spare CTAs go to the heaviest panels as extra row stripes
+// (one SM gathers at most ~226 random 128-byte rows per microsecond, see profiles/): stripes of a
+// panel sit in consecutive CTAs and the last one to arrive merges and commits.
 static int peel_persistent(const Plan& P, cudaStream_t s, const PeerTable* peers = nullptr) {
     const Layout& L = P.L;
-
     int dev = 0, sms = 0, per_sm = 0;
     EVX_CUDA(cudaGetDevice(&dev));
     EVX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    // Count planes go to shared memory when every CTA's share fits beside the merge buffer with two
-    // CTAs per SM; otherwise they stay in the workspace (L2-resident, touched only by their owner).
     const size_t base_smem = sizeof(PeelShared);
     const void* kernel = peers ? (const void*)k_peel_persistent<true> : (const void*)k_peel_persistent<false>;
     const size_t cp_bytes = sizeof(uint32_t) * (size_t)(L.kplanes + 1) * PW;
-    int target = sms * 2;
-    if (target > L.npl) target = L.npl;
-    if (target < 1) target = 1;
-    const size_t slots = (size_t)ceil_div(L.npl, target);
-    int planes_in_smem = (base_smem + slots * cp_bytes <= 112 * 1024) ? 1 : 0;
-    const size_t smem = base_smem + (planes_in_smem ? slots * cp_bytes : 0);
-    EVX_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    EVX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, PEEL_WARPS * 32, smem));
+    EVX_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(base_smem + 16 * 1024)));
+    EVX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, PEEL_WARPS * 32, base_smem + 16 * 1024));
     EVX_REQUIRE(per_sm >= 1, EVX_ERR_CUDA, "persistent peel kernel does not fit on an SM");
     int grid = sms * per_sm;
-    if (grid > target) grid = target;
-    if (planes_in_smem && (size_t)ceil_div(L.npl, grid) > slots) planes_in_smem = 0;   // fewer CTAs than planned
+    if (grid > PEEL_MAX_GRID) grid = PEEL_MAX_GRID;
+    const int npl = L.npl > 0 ? L.npl : 1;
+
+    // item table: items[slot * grid + cta]
+    std::vector<PeelItem> items;
+    int slots = 1, planes_in_smem = 0;
+    if (L.npl >= grid) {
+        slots = (int)ceil_div(L.npl, grid);
+        items.assign((size_t)slots * grid, PeelItem{-1, 0, 1, 0});
+        for (int q = 0; q < L.npl; ++q) {
+            const int slot = q / grid, r = q % grid;
+            const int cta = (slot & 1) ? (grid - 1 - r) : r;
+            items[(size_t)slot * grid + cta] = PeelItem{L.npl - 1 - q, 0, 1, slot};       // heaviest first
+        }
+        planes_in_smem = ((size_t)slots * cp_bytes <= 16 * 1024) ? 1 : 0;
+    } else {
+        // weights ~ rows a panel can see; stripes proportional to weight, every panel at least one
+        std::vector<int> st(npl, 1);
+        double wsum = 0;
+        for (int l = 0; l < npl; ++l) wsum += (double)(l * L.world + L.rank + 1);
+        int used = 0;
+        for (int l = 0; l < npl; ++l) {
+            int v = (int)((double)grid * (l * L.world + L.rank + 1) / wsum);
+            const int by_rows = (int)ceil_div((int64_t)(l * L.world + L.rank + 1) * TW, 32768);   // >= 32k potential rows each
+            if (v > by_rows) v = by_rows;
+            st[l] = v < 1 ? 1 : (v > PEEL_MAX_STRIPES ? PEEL_MAX_STRIPES : v);
+            used += st[l];
+        }
+        while (used > grid) {                                       // rounding overshoot: trim the lightest
+            for (int l = 0; l < npl && used > grid; ++l)
+                if (st[l] > 1) { --st[l]; --used; }
+        }
+        auto cap = [&](int l) {
+            const int by_rows = (int)ceil_div((int64_t)(l * L.world + L.rank + 1) * TW, 32768);
+            return by_rows < PEEL_MAX_STRIPES ? by_rows : PEEL_MAX_STRIPES;
+        };
+        for (int l = npl - 1; used < grid;) {                        // spare CTAs: heaviest panels first
+            if (st[l] < cap(l)) { ++st[l]; ++used; }
+            if (--l < 0) {
+                l = npl - 1;
+                bool room = false;
+                for (int t = 0; t < npl; ++t) room |= st[t] < cap(t);
+                if (!room) break;
+            }
+        }
+        grid = used;
+        items.assign((size_t)grid, PeelItem{-1, 0, 1, 0});
+        int cta = 0;
+        for (int l = npl - 1; l >= 0; --l)
+            for (int t = 0; t < st[l]; ++t) items[cta++] = PeelItem{l, t, st[l], 0};
+        bool split = false;
+        for (int l = 0; l < npl; ++l) split |= st[l] > 1;
+        planes_in_smem = (!split && cp_bytes <= 16 * 1024) ? 1 : 0;
+        if (L.npl == 0) items.assign(1, PeelItem{-1, 0, 1, 0});
+    }
+    const size_t smem = base_smem + (planes_in_smem ? (size_t)slots * cp_bytes : 0);
+    EVX_CUDA(cudaMemcpyAsync(P.at<PeelItem>(L.items), items.data(), sizeof(PeelItem) * items.size(),
+                             cudaMemcpyHostToDevice, s));
+    EVX_CUDA(cudaStreamSynchronize(s));                              // `items` is a pageable host buffer
+    EVX_CUDA(cudaMemsetAsync(P.at<unsigned int>(L.pdone), 0, sizeof(unsigned int) * 2 * (size_t)L.npl_max, s));
+
     const uint32_t* bits = P.at<uint32_t>(L.bits);
     const int* count = P.at<int>(L.count);
     int* rank_u = P.at<int>(L.rank_u);
@@ -1400,10 +1530,15 @@ static int peel_persistent(const Plan& P, cudaStream_t s, const PeerTable* peers
     int* fb = P.at<int>(L.flist2);
     Scal* scal = P.at<Scal>(L.scal);
     uint32_t* cpl = P.at<uint32_t>(L.cplanes);
-    int npl = L.npl, K = L.kplanes, world = L.world, rank = L.rank;
+    const PeelItem* ditems = P.at<PeelItem>(L.items);
+    uint32_t* partials = P.at<uint32_t>(L.partials);
+    unsigned int* pdone = P.at<unsigned int>(L.pdone);
+    unsigned int* pcommit = pdone + L.npl_max;
+    int K = L.kplanes, world = L.world, rank = L.rank;
     PeerTable pt{};
     if (peers) pt = *peers;
-    void* args[] = {&bits, &count, &rank_u, &fa, &fb, &scal, &cpl, &npl, &K, &world, &rank, &planes_in_smem, &pt};
+    void* args[] = {&bits, &count, &rank_u, &fa, &fb, &scal, &cpl, &ditems, &slots, &partials, &pdone, &pcommit, &K, &world,
+                    &rank, &planes_in_smem, &pt};
     EVX_CUDA(cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3(PEEL_WARPS * 32), args, smem, s));
     ++evx::launch_counter();
     return EVX_OK;
