@@ -29,7 +29,7 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--n", type=int, default=1_000_000)
+    ap.add_argument("--n", "--rows", dest="n", type=int, default=1_000_000)
     ap.add_argument("--m", type=int, default=3)
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])

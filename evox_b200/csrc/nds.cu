@@ -55,6 +55,7 @@ struct Scal {
     int xcnt[8];            // fused multi-rank peel: per-rank member counts of the current front
     int xtotal;             // fused multi-rank peel: their sum (-1: time-out)
     unsigned long long dbg[8];   // persistent peel: ns spent by CTA 0 / last CTA in accumulate, merge+commit, barrier
+    unsigned long long bdbg[8];  // world barrier, CTA 0: ns in {own fence+arrive, local wait, fence, send, peer wait, fence, release}
 };
 
 struct Layout {
@@ -788,31 +789,55 @@ __device__ __forceinline__ unsigned long long global_ns() {
 }
 constexpr unsigned long long PEER_TIMEOUT_NS = 4000000000ull;      // a peer that is 4 s late is gone
 
-// Barrier over all CTAs of all ranks.  Fills cnt_smem[r] with the number of members rank r published
+// Barrier over all CTAs of all ranks, which also carries the front exchange.  Publishers have written
+// this rank's new front members into the rank's OWN region only (local stores); once every local CTA
+// has arrived, CTA 0 pushes that region to every peer with coalesced stores, fences once at system
+// scope and sends one 64-bit message (epoch, member count) per peer, then waits for every peer's
+// message and releases the local CTAs.  Fills cnt_smem[r] with the number of members rank r published
 // for the coming front and returns their sum, or -1 after a time-out (every rank then leaves the
 // kernel; nothing spins forever).  `pub` is this rank's local publish counter for that front.
 __device__ __forceinline__ int world_barrier(Scal* scal, unsigned int& epoch, const PeerTable& pt, const int* pub,
-                                             int* cnt_smem, int* nf_smem) {
+                                             int which_next, int* cnt_smem, int* nf_smem) {
     __syncthreads();
     ++epoch;
+    const unsigned long long t0 = global_ns();
+    unsigned long long tb = t0, tn;
     if (threadIdx.x == 0) {
-        PeerState* me = peer_state(pt, pt.rank);
-        const unsigned long long t0 = global_ns();
-        bool dead = false;
-        __threadfence_system();                                       // this CTA's peer stores are out
+        __threadfence();                                              // this CTA's list stores are out (local memory)
         atomicAdd(&scal->barrier, 1u);
-        if (blockIdx.x == 0) {
+    }
+    if (blockIdx.x == 0) {
+        if (threadIdx.x == 0) {
+            tn = global_ns(); scal->bdbg[0] += tn - tb; tb = tn;
             unsigned int v;
             do {                                                      // every local CTA has arrived
                 asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&scal->barrier) : "memory");
             } while (v < epoch * gridDim.x);
-            __threadfence_system();
+            __threadfence();
             int mine;
             asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(mine) : "l"(pub) : "memory");
+            *nf_smem = mine;
+            tn = global_ns(); scal->bdbg[1] += tn - tb; tb = tn;
+        }
+        __syncthreads();
+        const int mine = *nf_smem;
+        const int* src = peer_region(pt, pt.rank, which_next, pt.rank);
+        for (int r = 0; r < pt.world; ++r) {                          // push my region to every peer over NVLink
+            if (r == pt.rank) continue;
+            int* dst = peer_region(pt, r, which_next, pt.rank);
+            for (int i = threadIdx.x; i < mine; i += blockDim.x) dst[i] = __ldcg(src + i);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            PeerState* me = peer_state(pt, pt.rank);
+            bool dead = false;
+            tn = global_ns(); scal->bdbg[2] += tn - tb; tb = tn;
+            __threadfence_system();                                   // the pushes are visible before the message
             const unsigned long long msg = ((unsigned long long)epoch << 32) | (unsigned int)mine;
             for (int r = 0; r < pt.world; ++r)                        // one message to every rank (and myself)
                 asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(&peer_state(pt, r)->xmsg[pt.rank]), "l"(msg)
                              : "memory");
+            tn = global_ns(); scal->bdbg[3] += tn - tb; tb = tn;
             int total = 0;
             for (int r = 0; r < pt.world && !dead; ++r) {             // wait for every rank's message
                 unsigned long long m;
@@ -827,7 +852,9 @@ __device__ __forceinline__ int world_barrier(Scal* scal, unsigned int& epoch, co
                 scal->xcnt[r] = c;
                 total += c;
             }
-            __threadfence_system();                                   // acquire: peers' list stores are visible
+            tn = global_ns(); scal->bdbg[4] += tn - tb; tb = tn;
+            __threadfence_system();                                   // acquire: peers' pushes are visible
+            tn = global_ns(); scal->bdbg[5] += tn - tb; tb = tn;
             if (dead) {
                 for (int r = 0; r < pt.world; ++r)
                     asm volatile("st.relaxed.sys.global.s32 [%0], %1;" ::"l"(&peer_state(pt, r)->abort), "r"(1) : "memory");
@@ -836,7 +863,12 @@ __device__ __forceinline__ int world_barrier(Scal* scal, unsigned int& epoch, co
             scal->xtotal = total;
             __threadfence();
             asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&scal->go), "r"(epoch) : "memory");
-        } else {
+            tn = global_ns(); scal->bdbg[6] += tn - tb; tb = tn;
+        }
+    }
+    if (threadIdx.x == 0) {
+        bool dead = false;
+        if (blockIdx.x != 0) {
             unsigned int v;
             do {
                 asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&scal->go) : "memory");
@@ -854,7 +886,7 @@ __device__ __forceinline__ int world_barrier(Scal* scal, unsigned int& epoch, co
 }
 
 // Warp 0, multi-rank: subtract, detect, retire, and write the new front members into this rank's
-// region of every rank's list.
+// own region (the barrier pushes the region to the peers).
 __device__ __forceinline__ void peel_commit_world(uint32_t* cp, int K, const uint32_t (*delta)[32], int pm, int lane,
                                                   int J, const PeerTable& pt, int which_next, int* pub,
                                                   uint32_t* newmask_out) {
@@ -886,15 +918,12 @@ __device__ __forceinline__ void peel_commit_world(uint32_t* cp, int K, const uin
     if (lane == 0) base = atomicAdd(pub, total);                      // local slot reservation
     base = __shfl_sync(0xFFFFFFFFu, base, 0) + incl - c;
     const int col0 = J * TW + lane * 32;
-    for (int r = 0; r < pt.world; ++r) {
-        int* dst = peer_region(pt, r, which_next, pt.rank) + base;
-        uint32_t w = nw;
-        int o = 0;
-        while (w) {
-            const int b = __ffs(w) - 1;
-            w &= w - 1;
-            dst[o++] = col0 + b;                                      // posted store over NVLink for r != rank
-        }
+    int* dst = peer_region(pt, pt.rank, which_next, pt.rank) + base;  // own region, own memory; CTA 0 pushes it
+    uint32_t w = nw;
+    while (w) {
+        const int b = __ffs(w) - 1;
+        w &= w - 1;
+        *dst++ = col0 + b;
     }
 }
 
@@ -1121,7 +1150,7 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
             if ((sh.newmask[c >> 5] >> (c & 31)) & 1u) rank_u[(size_t)l * TW + c] = 0;
         __syncthreads();
     }
-    int nf = MULTI ? world_barrier(scal, epoch, pt, &scal->pub3[0], sh.cnt, &sh.nf)
+    int nf = MULTI ? world_barrier(scal, epoch, pt, &scal->pub3[0], 0, sh.cnt, &sh.nf)
                    : grid_barrier(bar, epoch, &nf3[0], &sh.nf);
 
     // ---- fronts ----------------------------------------------------------------------------------
@@ -1239,12 +1268,18 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
                         for (int st2 = 0; st2 < ns; ++st2) {
                             if (st2 == it.stripe) continue;
                             const uint32_t* other = partials + ((size_t)(B - it.stripe + st2) * PEEL_PM_MAX) * 32;
+                            uint32_t o[PEEL_PM];                      // all planes in flight at once (L2 latency)
+#pragma unroll
+                            for (int p = 0; p < PEEL_PM; ++p) o[p] = (p < pm) ? __ldcg(other + p * 32 + lane) : 0u;
                             uint32_t carry = 0;
-                            for (int p = 0; p < pm; ++p) {
-                                const uint32_t a = sh.merge[0][p][lane], b2 = __ldcg(other + p * 32 + lane);
-                                const uint32_t x = a ^ b2;
-                                sh.merge[0][p][lane] = x ^ carry;
-                                carry = (a & b2) | (x & carry);
+#pragma unroll
+                            for (int p = 0; p < PEEL_PM; ++p) {
+                                if (p < pm) {
+                                    const uint32_t a = sh.merge[0][p][lane];
+                                    const uint32_t x = a ^ o[p];
+                                    sh.merge[0][p][lane] = x ^ carry;
+                                    carry = (a & o[p]) | (x & carry);
+                                }
                             }
                         }
                     }
@@ -1280,7 +1315,7 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
                 if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_mc += t - t_mark; t_mark = t; }
             }
         }
-        nf = MULTI ? world_barrier(scal, epoch, pt, &scal->pub3[(k + 1) % 3], sh.cnt, &sh.nf)
+        nf = MULTI ? world_barrier(scal, epoch, pt, &scal->pub3[(k + 1) % 3], (k + 1) & 1, sh.cnt, &sh.nf)
                    : grid_barrier(bar, epoch, &nf3[(k + 1) % 3], &sh.nf);
         if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_bar += t - t_mark; t_mark = t; }
     }
@@ -1658,7 +1693,7 @@ extern "C" int evx_nds_shard_peel_fused(evx_nds_shard* p, void* const* peer_bufs
 extern "C" int evx_debug_peel_times(evx_nds_shard* p, uint64_t* out8) {
     EVX_REQUIRE(p && out8, EVX_ERR_ARG, "evx_debug_peel_times: null argument");
     Scal* scal = p->P.at<Scal>(p->P.L.scal);
-    EVX_CUDA(cudaMemcpy(out8, scal->dbg, sizeof(uint64_t) * 8, cudaMemcpyDeviceToHost));
+    EVX_CUDA(cudaMemcpy(out8, scal->dbg, sizeof(uint64_t) * 16, cudaMemcpyDeviceToHost));
     return EVX_OK;
 }
 

@@ -38,10 +38,13 @@ t = torch.tensor(acc, device="cuda"); mx = t.clone(); dist.all_reduce(mx, op=dis
 if rank == 0:
     names = ["build(sort+tiles)", "init+host barrier", "fused peel kernel", "rank scatter", "all_reduce ranks"]
     for nm, a, b in zip(names, mn.tolist(), mx.tolist()): print(f"{nm:22s} min {a:8.3f} ms  max {b:8.3f} ms")
-    dbg = (ctypes.c_uint64 * 8)()
+    dbg = (ctypes.c_uint64 * 16)()
     check(L.evx_debug_peel_times(f.shard.plan, dbg))
     for nm, o in (("first CTA", 0), ("last CTA", 4)):
         k = max(1, dbg[o + 3])
         print(f"{nm}: per front  accumulate {dbg[o]/k/1e3:7.2f} us  merge+commit {dbg[o+1]/k/1e3:6.2f} us  barrier {dbg[o+2]/k/1e3:6.2f} us")
+    k = max(1, dbg[3])
+    names2 = ["own arrive", "local wait", "push to peers", "fence.sys+send", "peer wait", "fence.sys(acq)", "release"]
+    print("world barrier, CTA 0, us per front: " + ", ".join(f"{n} {dbg[8+i]/k/1e3:.2f}" for i, n in enumerate(names2)))
     print("fronts", f.num_fronts, "world", world, "n", n, flush=True)
 dist.destroy_process_group()
