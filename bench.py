@@ -270,10 +270,25 @@ def run_ours(args):
     if stages:
         t = stages["tiles"] * 1e-3
         alg_bytes = pairs / 8.0                       # one bit emitted per ordered pair (1 bit written)
+        headline = (n == 1_000_000 and m == 3)        # the ncu DRAM counters in profiles/ are for this shape
         line["roofline"] = {"bound": "hbm", "kernel": "k_dominance_tiles", "achieved": alg_bytes / t / 1e9, "peak": hbm_peak,
-                            "unit": "GB/s", "frac": alg_bytes / t / 1e9 / hbm_peak, "traffic": None,
+                            "unit": "GB/s", "frac": alg_bytes / t / 1e9 / hbm_peak,
+                            "traffic": 65.03e9 if headline else None,
+                            "traffic_source": "profiles/r1_final_traffic_n1m.csv (dram read 2.47 GB + write 62.57 GB per launch)"
+                            if headline else None,
                             "peak_source": peak_src, "ms_per_launch": stages["tiles"],
-                            "note": "compare-issue bound, not HBM bound (SURVEY 8d); see compare_roofline"}
+                            "note": "algorithmic bytes = N^2/8 (one bit per ordered pair of the reference's N x N relation); the "
+                                    "kernel stores only the half that can be non-zero and is instruction-issue bound, not HBM "
+                                    "bound (SURVEY 8d): see compare_roofline"}
+        tp = stages["peel"] * 1e-3
+        peel_bytes = pairs / 16.0                     # every stored bit is read exactly once by the peel
+        line["peel_roofline"] = {"bound": "hbm", "kernel": "k_peel_persistent", "achieved": peel_bytes / tp / 1e9,
+                                 "peak": hbm_peak, "unit": "GB/s", "frac": peel_bytes / tp / 1e9 / hbm_peak,
+                                 "traffic": 62.70e9 if headline else None, "ms_per_launch": stages["peel"],
+                                 "random_gather_peak": 4290.0,
+                                 "frac_of_random_gather_peak": peel_bytes / tp / 1e9 / 4290.0,
+                                 "note": "random 128-byte row gathers: tools/probes/gather_probe.cu measures 4.29 TB/s as the "
+                                         "ceiling of that access pattern on this GPU (profiles/r1_gather_probe.txt)"}
         line["stages_ms"] = stages
         try:
             pr = ctypes.c_double()
