@@ -303,6 +303,7 @@ def run_ours(args):
             line["compare_roofline"] = {"error": str(e)}
     if world == 1 and not args.no_nsga2:
         line["nsga2"] = nsga2_gens_per_s(torch)
+        line["operators"] = operator_rates(torch, hbm_peak)
     if not args.no_cpu_baseline:
         ns = auto_cpu_sample(m, args.seed, user=args.cpu_sample)
         _, dt1, _ = cpu_oracle_rate(ns, m, args.seed)
@@ -314,6 +315,47 @@ def run_ours(args):
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def operator_rates(torch, hbm_peak):
+    """The other rows of the hot path (crowding keys/s, evals/s), inputs resident, CUDA events,
+    median of 10 after 3 warm-ups.  GB/s figures use the algorithmic bytes of DESIGN.md section 4."""
+    import evox_b200 as E
+    g = torch.Generator(device="cuda").manual_seed(1)
+
+    def med(fn, reps=10):
+        for _ in range(3):
+            fn()
+        ts = []
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); fn(); e1.record(); torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        ts.sort()
+        return ts[len(ts) // 2] * 1e-3
+
+    out = {}
+    n, m = 200_000, 3
+    F = torch.rand((n, m), device="cuda", generator=g)
+    t = med(lambda: E.operators.crowding_distance(F))
+    out["crowding_distance"] = {"workload": f"N={n} M={m} mask=None", "keys_per_s": n * m / t, "ms": t * 1e3,
+                                "GB/s": (4 * n * m + 4 * n) / t / 1e9}
+    mask = torch.rand(n, device="cuda", generator=g) < 0.02
+    t = med(lambda: E.operators.crowding_distance(F, mask))
+    out["crowding_distance_masked"] = {"workload": f"N={n} M={m} mask = 2% (a cut front)", "keys_per_s": n * m / t,
+                                       "ms": t * 1e3}
+    x = torch.rand((16384, 3), device="cuda", generator=g)
+    t = med(lambda: E.utils.dominate_relation(x, x))
+    out["dominate_relation"] = {"workload": "16384 x 16384, M=3, bool matrix out", "pairs_per_s": 16384.0 ** 2 / t,
+                                "GB/s": 16384.0 ** 2 / t / 1e9, "frac_of_hbm_peak": 16384.0 ** 2 / t / 1e9 / hbm_peak, "ms": t * 1e3}
+    for name, nn, d, mm in (("DTLZ2", 100_000, 12, 3), ("MaF1", 50_000, 19, 10), ("LSMOP1", 100_000, 300, 3)):
+        X = torch.rand((nn, d), device="cuda", generator=g)
+        prob = getattr(E.problems.numerical, name)(d=d, m=mm)
+        t = med(lambda: prob.evaluate(None, X))
+        b = 4.0 * nn * (d + mm)
+        out[f"evaluate_{name}"] = {"workload": f"n={nn} d={d} m={mm}", "evals_per_s": nn / t, "GB/s": b / t / 1e9,
+                                   "frac_of_hbm_peak": b / t / 1e9 / hbm_peak, "us": t * 1e6}
+    return out
 
 
 def nsga2_gens_per_s(torch, pop=100_000, d=12, m=3, gens=10):

@@ -12,9 +12,10 @@ constexpr int REL_TX = 128;      // threads per CTA
 constexpr int REL_ROWS = 32;     // x rows per CTA
 constexpr int REL_CPT = 16;      // y columns per thread (16 bytes of output per row)
 
-// out[i, j] byte matrix.  Thread <-> 16 consecutive columns (values in registers when M <= 4, else
-// re-read from L1), CTA <-> 32 rows staged in shared memory.  Each warp writes 512 contiguous bytes
-// of one output row per step: the kernel is bound by the nx*ny-byte store stream.
+// out[i, j] byte matrix.  Thread <-> 16 consecutive columns whose M objectives sit in registers
+// (M <= 4; larger M re-reads them through L1), CTA <-> 32 rows staged in shared memory and broadcast.
+// Each warp writes 512 contiguous bytes of one output row per step: the kernel is bound by the
+// nx*ny-byte store stream the reference API demands, then by FSETP issue (2*M compares per pair).
 template <int M>
 __global__ void __launch_bounds__(REL_TX)
 k_relation_u8(const float* __restrict__ x, int64_t nx, const float* __restrict__ y, int64_t ny, int m_rt,
@@ -29,33 +30,54 @@ k_relation_u8(const float* __restrict__ x, int64_t nx, const float* __restrict__
     if (j0 >= ny) return;
     const int ncol = (int)min((int64_t)REL_CPT, ny - j0);
     const bool vec_ok = (ncol == REL_CPT) && ((ny & 15) == 0) && ((reinterpret_cast<size_t>(out) & 15) == 0);
-    for (int r = 0; r < rows; ++r) {
-        uint32_t pk[4] = {0, 0, 0, 0};
-        for (int c = 0; c < ncol; ++c) {
-            const float* yj = y + (j0 + c) * m;
-            bool le = true, lt = false;
+    if constexpr (M > 0) {
+        float yv[REL_CPT][M];
 #pragma unroll
-            for (int k = 0; k < (M > 0 ? M : 1); ++k) {
-                if (M > 0) {
-                    const float a = xs[r * m + k], b = __ldg(yj + k);
-                    le = le && (a <= b);
-                    lt = lt || (a < b);
+        for (int c = 0; c < REL_CPT; ++c)
+#pragma unroll
+            for (int k = 0; k < M; ++k)
+                yv[c][k] = (c < ncol) ? __ldg(y + (j0 + c) * M + k) : __int_as_float(0x7FC00000);   // NaN: never dominated
+        for (int r = 0; r < rows; ++r) {
+            float a[M];
+#pragma unroll
+            for (int k = 0; k < M; ++k) a[k] = xs[r * M + k];
+            uint32_t pk[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int c = 0; c < REL_CPT; ++c) {
+                bool le = true, ge = true;                            // any(a < b) == !all(a >= b) once all(a <= b) holds
+#pragma unroll
+                for (int k = 0; k < M; ++k) {
+                    le = le && (a[k] <= yv[c][k]);
+                    ge = ge && (a[k] >= yv[c][k]);
                 }
+                pk[c >> 2] |= (uint32_t)(le && !ge) << (8 * (c & 3));
             }
-            if (M == 0) {
+            uint8_t* o = out + (row0 + r) * ny + j0;
+            if (vec_ok) {
+                *reinterpret_cast<uint4*>(o) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            } else {
+                for (int c = 0; c < ncol; ++c) o[c] = (uint8_t)((pk[c >> 2] >> (8 * (c & 3))) & 0xFF);
+            }
+        }
+    } else {
+        for (int r = 0; r < rows; ++r) {
+            uint32_t pk[4] = {0, 0, 0, 0};
+            for (int c = 0; c < ncol; ++c) {
+                const float* yj = y + (j0 + c) * m;
+                bool le = true, lt = false;
                 for (int k = 0; k < m; ++k) {
                     const float a = xs[r * m + k], b = __ldg(yj + k);
                     le = le && (a <= b);
                     lt = lt || (a < b);
                 }
+                pk[c >> 2] |= (uint32_t)(le && lt) << (8 * (c & 3));
             }
-            pk[c >> 2] |= (uint32_t)(le && lt) << (8 * (c & 3));
-        }
-        uint8_t* o = out + (row0 + r) * ny + j0;
-        if (vec_ok) {
-            *reinterpret_cast<uint4*>(o) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-        } else {
-            for (int c = 0; c < ncol; ++c) o[c] = (uint8_t)((pk[c >> 2] >> (8 * (c & 3))) & 0xFF);
+            uint8_t* o = out + (row0 + r) * ny + j0;
+            if (vec_ok) {
+                *reinterpret_cast<uint4*>(o) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            } else {
+                for (int c = 0; c < ncol; ++c) o[c] = (uint8_t)((pk[c >> 2] >> (8 * (c & 3))) & 0xFF);
+            }
         }
     }
 }
