@@ -33,9 +33,9 @@ namespace evx {
 constexpr int TW = 1024;            // columns per panel
 constexpr int PW = TW / 32;         // words per panel row (128 B)
 constexpr int RB = 2;               // rows per lane in the tile kernel
-constexpr int TILE_WARPS = 4;
+constexpr int TILE_WARPS = 8;
 constexpr int SLAB = 32 * RB;       // rows per warp and pass
-constexpr int MAX_SLABS = 4;        // passes per warp (count planes stay in registers across passes)
+constexpr int MAX_SLABS = 2;        // passes per warp (count planes stay in registers across passes)
 constexpr int APPLY_WARPS = 8;
 constexpr int PEEL_MAX_GRID = 1024;  // upper bound on the CTAs of the persistent peel kernel
 constexpr int PEEL_PM_MAX = 16;      // >= merged count planes of the persistent peel (PEEL_PM)
@@ -325,10 +325,10 @@ __device__ __forceinline__ uint32_t f2_mask(const float* c, float r) {
     return pos >= 32 ? 0u : (0xFFFFFFFFu << pos);
 }
 
-constexpr int TILE_NUP = 6;                            // count planes 8 .. 256 (MAX_SLABS * SLAB rows)
+constexpr int TILE_NUP = 5;                            // count planes 8 .. 128 (MAX_SLABS * SLAB = 128 rows)
 
 struct CountPlanes {
-    uint32_t ones = 0, twos = 0, fours = 0, up[TILE_NUP] = {0, 0, 0, 0, 0, 0};
+    uint32_t ones = 0, twos = 0, fours = 0, up[TILE_NUP] = {0, 0, 0, 0, 0};
 };
 
 // Copy one staged slab out (lane <-> word column: full 128-byte lines) and fold it into the planes.
@@ -385,20 +385,20 @@ __device__ __forceinline__ void tile_offdiag(const float* __restrict__ ucols, in
                                              int row0, int rowlimit, int slabs, uint32_t* __restrict__ bits,
                                              int* __restrict__ count, int world, int rank, uint32_t* smem) {
     constexpr int CR = (M > 3) ? M - 3 : 0;
+    constexpr int NF = (M > 1) ? M - 1 : 1;                                // staged objective arrays
     float* f1s = reinterpret_cast<float*>(smem);                           // [TW]
-    float* f2s = f1s + TW;                                                 // [TW]
+    float* f2s = f1s + ((M >= 3) ? TW : 0);                                // [TW]
     float* rest = f2s + TW;                                                // [TW][CR]
-    uint32_t* stage = smem + M * TW;                                       // [TILE_WARPS][PW][SLAB+1]
-    int* scount = reinterpret_cast<int*>(stage + TILE_WARPS * PW * (SLAB + 1));   // [TW]
-    float* wmin = reinterpret_cast<float*>(scount + TW);                   // [PW] f1 range of each word
+    uint32_t* stage = smem + NF * TW;                                      // [TILE_WARPS][PW][SLAB+1]
+    float* wmin = reinterpret_cast<float*>(stage + TILE_WARPS * PW * (SLAB + 1));   // [PW] f1 range of each word
     float* wmax = wmin + PW;
+    int* scount = reinterpret_cast<int*>(smem);                            // [TW], reuses f1s once the slabs are done
 
     for (int t = threadIdx.x; t < TW; t += blockDim.x) {
         if constexpr (M >= 2) f1s[t] = ucols[npad + col0 + t];
         if constexpr (M >= 3) f2s[t] = ucols[2 * npad + col0 + t];
 #pragma unroll
         for (int k = 0; k < CR; ++k) rest[t * CR + k] = ucols[(int64_t)(3 + k) * npad + col0 + t];
-        scount[t] = 0;
     }
     __syncthreads();
     if constexpr (M >= 2) {
@@ -485,6 +485,9 @@ __device__ __forceinline__ void tile_offdiag(const float* __restrict__ ucols, in
         slab_out(st + lane * (SLAB + 1), bits + d_panel_words_before(l, world, rank) + (int64_t)rs * PW, lane, cp);
         __syncwarp();
     }
+    __syncthreads();                                                       // every warp is done with f1s
+    for (int t = threadIdx.x; t < TW; t += blockDim.x) scount[t] = 0;
+    __syncthreads();
     counts_flush(cp, any_rows, lane, scount, count, l);
 }
 
@@ -554,6 +557,7 @@ __device__ __forceinline__ void tile_diag(const float* __restrict__ ucols, int64
     counts_flush(cp, any_rows, lane, scount, count, l);
 }
 
+// Off-diagonal tiles: grid = (row chunks, owned panels); chunks at or past the panel's own block leave.
 template <int M>
 __global__ void __launch_bounds__(TILE_WARPS * 32)
 k_dominance_tiles(const float* __restrict__ ucols, int64_t npad, const Scal* __restrict__ scal,
@@ -563,12 +567,27 @@ k_dominance_tiles(const float* __restrict__ ucols, int64_t npad, const Scal* __r
     const int U = scal->U;
     const int col0 = J * TW;
     if (col0 >= U) return;
-    const int rowlimit = min((J + 1) * TW, U);
     const int row0 = blockIdx.x * (slabs * TILE_WARPS * SLAB);
+    if (row0 >= col0) return;
+    extern __shared__ __align__(16) uint32_t smem[];
+    tile_offdiag<M>(ucols, npad, U, l, col0, row0, col0, slabs, bits, count, world, rank, smem);
+}
+
+// Diagonal tiles: grid = (row chunks of one block, owned panels).
+template <int M>
+__global__ void __launch_bounds__(TILE_WARPS * 32)
+k_dominance_diag(const float* __restrict__ ucols, int64_t npad, const Scal* __restrict__ scal,
+                 uint32_t* __restrict__ bits, int* __restrict__ count, int world, int rank, int slabs) {
+    const int l = blockIdx.y;
+    const int J = l * world + rank;
+    const int U = scal->U;
+    const int col0 = J * TW;
+    if (col0 >= U) return;
+    const int rowlimit = min((J + 1) * TW, U);
+    const int row0 = col0 + blockIdx.x * (slabs * TILE_WARPS * SLAB);
     if (row0 >= rowlimit) return;
     extern __shared__ __align__(16) uint32_t smem[];
-    if (row0 >= col0) tile_diag<M>(ucols, npad, U, l, col0, row0, rowlimit, slabs, bits, count, world, rank, smem);
-    else tile_offdiag<M>(ucols, npad, U, l, col0, row0, rowlimit, slabs, bits, count, world, rank, smem);
+    tile_diag<M>(ucols, npad, U, l, col0, row0, rowlimit, slabs, bits, count, world, rank, smem);
 }
 
 // Fallback for M > MAX_TEMPLATE_M: same labelling and layout, objective loop at run time.
@@ -1351,16 +1370,26 @@ struct Plan {
 template <int M>
 static int launch_tiles(const Plan& P, cudaStream_t s) {
     const Layout& L = P.L;
-    const size_t smem = sizeof(uint32_t) * ((size_t)M * TW + (size_t)TILE_WARPS * PW * (SLAB + 1) + TW + 2 * PW);
+    const size_t stage_words = (size_t)TILE_WARPS * PW * (SLAB + 1);
+    const size_t smem = sizeof(uint32_t) * ((size_t)(M > 1 ? M - 1 : 1) * TW + stage_words + 2 * PW);
+    const size_t smem_diag = sizeof(uint32_t) * ((size_t)M * TW + stage_words + TW);
     EVX_CUDA(cudaFuncSetAttribute(k_dominance_tiles<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    EVX_CUDA(cudaFuncSetAttribute(k_dominance_diag<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_diag));
     // rows per CTA = slabs * TILE_WARPS * SLAB (256 .. 1024, always dividing TW): as many passes per
     // warp as still leave a few waves of CTAs on the chip
     int slabs = MAX_SLABS;
     while (slabs > 1 && (int64_t)L.npl * L.np * (TW / (slabs * TILE_WARPS * SLAB)) / 2 < 148 * 5 * 4) slabs >>= 1;
     dim3 grid((unsigned)ceil_div(L.npad, slabs * TILE_WARPS * SLAB), (unsigned)L.npl);
-    k_dominance_tiles<M><<<grid, TILE_WARPS * 32, smem, s>>>(P.at<float>(L.ucols), L.npad, P.at<Scal>(L.scal),
-                                                              P.at<uint32_t>(L.bits), P.at<int>(L.count), L.world,
-                                                              L.rank, slabs);
+    if (L.np > 1) {
+        k_dominance_tiles<M><<<grid, TILE_WARPS * 32, smem, s>>>(P.at<float>(L.ucols), L.npad, P.at<Scal>(L.scal),
+                                                                  P.at<uint32_t>(L.bits), P.at<int>(L.count), L.world,
+                                                                  L.rank, slabs);
+        EVX_LAUNCH_CHECK();
+    }
+    dim3 gdiag((unsigned)ceil_div(TW, slabs * TILE_WARPS * SLAB), (unsigned)L.npl);
+    k_dominance_diag<M><<<gdiag, TILE_WARPS * 32, smem_diag, s>>>(P.at<float>(L.ucols), L.npad, P.at<Scal>(L.scal),
+                                                                   P.at<uint32_t>(L.bits), P.at<int>(L.count), L.world,
+                                                                   L.rank, slabs);
     EVX_LAUNCH_CHECK();
     return EVX_OK;
 }
