@@ -303,6 +303,7 @@ def run_ours(args):
             line["compare_roofline"] = {"error": str(e)}
     if world == 1 and not args.no_nsga2:
         line["nsga2"] = nsga2_gens_per_s(torch)
+        line["nsga2_small"] = nsga2_gens_per_s(torch, pop=100, d=7, m=3, gens=100, problem="DTLZ1")   # configs[0] shape
         line["operators"] = operator_rates(torch, hbm_peak)
     if not args.no_cpu_baseline:
         ns = auto_cpu_sample(m, args.seed, user=args.cpu_sample)
@@ -358,13 +359,13 @@ def operator_rates(torch, hbm_peak):
     return out
 
 
-def nsga2_gens_per_s(torch, pop=100_000, d=12, m=3, gens=10):
+def nsga2_gens_per_s(torch, pop=100_000, d=12, m=3, gens=10, problem="DTLZ2"):
     """Second half of BASELINE.json's metric: NSGA-II generations/s at pop 100k on DTLZ2 (configs[2]):
     variation kernel -> DTLZ2 evaluate -> concat -> non_dominate(2*pop -> pop), all on the device."""
     import evox_b200 as E
     from evox_b200.algorithms import NSGA2, run_generations
     alg = NSGA2(torch.zeros(d), torch.ones(d), n_objs=m, pop_size=pop)
-    prob = E.problems.numerical.DTLZ2(d=d, m=m)
+    prob = getattr(E.problems.numerical, problem)(d=d, m=m)
     state = alg.setup(seed=0)
     state, _ = run_generations(alg, prob, state, 3)                    # warm-up (first fronts are the deepest)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -375,7 +376,7 @@ def nsga2_gens_per_s(torch, pop=100_000, d=12, m=3, gens=10):
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
     return {"metric": "nsga2_generations_per_s", "value": gens / (ms * 1e-3), "unit": "generations/s",
-            "ms_per_generation": ms / gens, "config": {"workload": f"NSGA-II DTLZ2 d={d} M={m} pop={pop} (merged N={2 * pop})",
+            "ms_per_generation": ms / gens, "config": {"workload": f"NSGA-II {problem} d={d} M={m} pop={pop} (merged N={2 * pop})",
                                                        "generations_timed": gens, "after_warmup_generations": 3},
             "note": "variation = evx_variation_sbx_pm_f32 (Philox; statistical parity with jax.random), "
                     "selection glue = torch sorts as in non_dominate.py:210-222"}

@@ -62,6 +62,10 @@ __device__ __forceinline__ uint32_t float_key_nan_last(float v) {
     return (v != v) ? 0xFFFFFFFFu : float_key(v);
 }
 
+// Small-population non-dominated sort (nds_small.cu): n <= 4096 rows, scratch = n*words uint32 + n int.
+int small_nds_launch(const float* x, int n, int m, int* rank, uint32_t* bits, int words, int* count, int* fronts_out,
+                     cudaStream_t s);
+
 // Grow-only device arena for the *_host_* entry points (one per device, mutex-guarded).
 int arena_get(size_t bytes, void** ptr);
 

@@ -37,6 +37,7 @@ constexpr int TILE_WARPS = 8;
 constexpr int SLAB = 32 * RB;       // rows per warp and pass
 constexpr int MAX_SLABS = 2;        // passes per warp (count planes stay in registers across passes)
 constexpr int APPLY_WARPS = 8;
+constexpr int SMALL_PATH_MAX_N = 1024;   // populations of at most one panel take the direct small path
 constexpr int PEEL_MAX_GRID = 1024;  // upper bound on the CTAs of the persistent peel kernel
 constexpr int PEEL_PM_MAX = 16;      // >= merged count planes of the persistent peel (PEEL_PM)
 constexpr int ANY_SLOTS = 64;
@@ -1742,6 +1743,21 @@ extern "C" int evx_nds_f32(const float* x, int64_t n, int32_t m, int32_t* rank, 
     Plan P;
     P.L = make_layout(n, m, 1, 0);
     P.ws = reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(ws), 256));
+    if (n <= SMALL_PATH_MAX_N && !use_stepwise_peel()) {
+        // At most one panel: the sort / tile / persistent-peel pipeline is all launch latency here.
+        // Direct n x n test + single-CTA peel: three launches (measured 30 us at n = 200 against 235 us).
+        const int words = (int)ceil_div(n, 32);
+        Scal* scal = P.at<Scal>(P.L.scal);
+        int rc = small_nds_launch(x, (int)n, m, rank, P.at<uint32_t>(P.L.bits), words, P.at<int>(P.L.count),
+                                  &scal->fronts, s);
+        if (rc) return rc;
+        int fronts = 0;
+        EVX_CUDA(cudaMemcpyAsync(&fronts, &scal->fronts, sizeof(int), cudaMemcpyDeviceToHost, s));
+        EVX_CUDA(cudaStreamSynchronize(s));
+        g_last_fronts = fronts;
+        g_prof.have = false;
+        return EVX_OK;
+    }
     Prof& pf = g_prof;
     pf.have = false;
     if (pf.on) {

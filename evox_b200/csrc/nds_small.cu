@@ -59,7 +59,7 @@ __global__ void k_small_clear(int* __restrict__ count, int n) {
 // Lane <-> column j, warp <-> 8 rows: one ballot per (row, 32 columns).  Full definition of
 // dominance (utils/common.py:88-91), no pre-sort: n is small.
 __global__ void __launch_bounds__(256)
-k_small_bits(const float* __restrict__ x, int n, int m, uint32_t* __restrict__ bits, int* __restrict__ count) {
+k_small_bits(const float* __restrict__ x, int n, int m, int words, uint32_t* __restrict__ bits, int* __restrict__ count) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int j = blockIdx.x * 32 + lane;
     const int r0 = blockIdx.y * 64 + warp * 8;
@@ -74,7 +74,7 @@ k_small_bits(const float* __restrict__ x, int n, int m, uint32_t* __restrict__ b
         }
         const bool d = le && lt;
         const uint32_t w = __ballot_sync(0xFFFFFFFFu, d);
-        if (lane == 0) bits[(size_t)r * SMALL_WORDS + blockIdx.x] = w;
+        if (lane == 0) bits[(size_t)r * words + blockIdx.x] = w;
         cnt += d;
     }
     if (cnt) atomicAdd(&count[j], cnt);
@@ -82,7 +82,8 @@ k_small_bits(const float* __restrict__ x, int n, int m, uint32_t* __restrict__ b
 
 // One CTA peels every front: no host round trip, no grid-wide barrier.
 __global__ void __launch_bounds__(1024)
-k_small_peel(const uint32_t* __restrict__ bits, int* __restrict__ count, int n, int* __restrict__ rank) {
+k_small_peel(const uint32_t* __restrict__ bits, int* __restrict__ count, int n, int words, int* __restrict__ rank,
+             int* __restrict__ fronts_out) {
     __shared__ int front[SMALL_MAX_N];
     __shared__ int nf;
     constexpr int PER = SMALL_MAX_N / 1024;
@@ -100,18 +101,35 @@ k_small_peel(const uint32_t* __restrict__ bits, int* __restrict__ count, int n, 
         }
         __syncthreads();
         const int f = nf;
-        if (f == 0) break;
+        if (f == 0) {
+            if (threadIdx.x == 0 && fronts_out) *fronts_out = k;
+            break;
+        }
 #pragma unroll
         for (int t = 0; t < PER; ++t) {
             const int j = threadIdx.x + t * 1024;
             if (j < n && count[j] > 0) {
                 int dec = 0;
-                for (int q = 0; q < f; ++q) dec += (bits[(size_t)front[q] * SMALL_WORDS + (j >> 5)] >> (j & 31)) & 1u;
+                for (int q = 0; q < f; ++q) dec += (bits[(size_t)front[q] * words + (j >> 5)] >> (j & 31)) & 1u;
                 count[j] -= dec;
             }
         }
         __syncthreads();
     }
+}
+
+// Shared by evx_nds_noalloc_f32 (built-in scratch) and by evx_nds_f32 for populations of at most one
+// panel (scratch inside the caller's workspace): three launches, no host round trip.
+int small_nds_launch(const float* x, int n, int m, int* rank, uint32_t* bits, int words, int* count, int* fronts_out,
+                     cudaStream_t s) {
+    k_small_clear<<<(n + 255) / 256, 256, 0, s>>>(count, n);
+    EVX_LAUNCH_CHECK();
+    dim3 grid((n + 31) / 32, (n + 63) / 64);
+    k_small_bits<<<grid, 256, 0, s>>>(x, n, m, words, bits, count);
+    EVX_LAUNCH_CHECK();
+    k_small_peel<<<1, 1024, 0, s>>>(bits, count, n, words, rank, fronts_out);
+    EVX_LAUNCH_CHECK();
+    return EVX_OK;
 }
 
 }  // namespace evx
@@ -129,14 +147,5 @@ extern "C" int evx_nds_noalloc_f32(const float* x, int64_t n, int32_t m, int32_t
     SmallScratch* sc = nullptr;
     int rc = small_scratch(&sc);
     if (rc) return rc;
-    cudaStream_t s = (cudaStream_t)stream;
-    const int ni = (int)n;
-    k_small_clear<<<(ni + 255) / 256, 256, 0, s>>>(sc->count, ni);
-    EVX_LAUNCH_CHECK();
-    dim3 grid((ni + 31) / 32, (ni + 63) / 64);
-    k_small_bits<<<grid, 256, 0, s>>>(x, ni, m, sc->bits, sc->count);
-    EVX_LAUNCH_CHECK();
-    k_small_peel<<<1, 1024, 0, s>>>(sc->bits, sc->count, ni, rank);
-    EVX_LAUNCH_CHECK();
-    return EVX_OK;
+    return small_nds_launch(x, (int)n, m, rank, sc->bits, SMALL_WORDS, sc->count, nullptr, (cudaStream_t)stream);
 }

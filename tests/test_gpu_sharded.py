@@ -73,3 +73,33 @@ def test_stepwise_peel_env_switch(monkeypatch):
     monkeypatch.setenv("EVX_PEEL", "stepwise")
     b = E.operators.non_dominated_sort(x)
     assert torch.equal(a, b)
+
+
+def test_fused_peel_world_of_one():
+    """The fused multi-rank peel kernel (peer-mapped lists, world-wide barrier) with a process group of
+    one rank: same kernel and protocol as on 8 GPUs, peers == self.  Multi-GPU runs are exercised by
+    tools/fused_check.py under torchrun (see profiles/r1_scaling.md)."""
+    import os
+    import torch.distributed as dist
+    from oracle import oracle_c as C
+    from evox_b200.distributed import FusedShardedNonDominatedSort
+    created = False
+    if not dist.is_initialized():
+        port = 29600 + os.getpid() % 300
+        dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=0, world_size=1,
+                                device_id=torch.device("cuda", torch.cuda.current_device()))
+        created = True
+    try:
+        try:
+            f = FusedShardedNonDominatedSort(30000, 3)
+        except (ImportError, RuntimeError, AttributeError) as e:     # no symmetric memory on this box
+            pytest.skip(f"torch symmetric memory unavailable: {e}")
+        x = np.random.default_rng(6).random((30000, 3), dtype=np.float32)
+        x[:500] = x[500:1000]
+        ref = C.non_dominated_sort(x)
+        for _ in range(2):
+            got = f(torch.from_numpy(x).cuda())
+            assert (got.cpu().numpy() == ref).all() and f.num_fronts == int(ref.max()) + 1
+    finally:
+        if created:
+            dist.destroy_process_group()
