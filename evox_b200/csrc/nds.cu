@@ -8,16 +8,22 @@
 //   2. The remaining rows are sorted lexicographically by (f0, f1, ..) on order-preserving integer
 //      keys (-0 folded onto +0) and de-duplicated: equal rows dominate nothing among themselves and
 //      have identical dominator sets, hence identical ranks.  U unique rows remain.
-//   3. For unique rows i, j in sorted order: i dominates j  <=>  i < j and f_k[i] <= f_k[j] for all
-//      k >= 1  (f0 is implied by the order; strictness by uniqueness).  Only the strict upper
-//      triangle exists, and each pair costs M-1 compares.
-//   4. The bit matrix is stored by column PANELS of TW = 1024 columns: panel J holds rows
-//      0 .. (J+1)*TW-1, each row PW = 32 words (128 B).  Packed triangular: N^2/16 bytes.  A panel
-//      is owned by one rank (J mod world) and, inside a rank, by whoever processes that panel, so
-//      dominator counts of a panel's columns are private to its owner.
-//   5. Peeling: front k = columns whose count is 0.  Every front row is read exactly once per
-//      panel (128 B line), rows are summed bit-sliced (carry-save adders), and the per-column sums
-//      are subtracted from the counts.  Total peel traffic = the matrix, once.
+//   3. Labels: blocks of TW = 1024 consecutive lexicographic positions; inside a block rows are
+//      ordered by f1; inside each run of 32 (one bit-matrix word) by f2.
+//   4. For labelled rows i, j: block(i) < block(j)  =>  i dominates j  <=>  f_k[i] <= f_k[j] for all
+//      k >= 1 (f0 by the order, strictness by uniqueness); block(i) > block(j) => never; same block:
+//      all M objectives.  Only the block-upper triangle exists.
+//   5. Tiles: a 64-row slab against a 32-column word is classified by its f1 ranges (skip / f1
+//      passes / mixed); f2 is a binary-searched suffix mask; what remains is compared on the FMA
+//      pipe (sign of b - a).
+//   6. The bit matrix is stored by column PANELS of TW columns: panel J holds rows 0 .. (J+1)*TW-1,
+//      each row PW = 32 words (128 B).  Packed: N^2/16 bytes.  A panel and the dominator counts of
+//      its columns are owned by one rank (J mod world).
+//   7. Peeling: front k = columns whose count is 0.  Every front row is read exactly once per panel
+//      (one 128-byte bulk copy), rows are summed bit-sliced (carry-save adders), subtracted from
+//      bit-sliced counts, and "count == 0" is the NOR of the planes.  One persistent cooperative
+//      kernel peels all fronts; on several GPUs the same kernel also exchanges front membership over
+//      NVLink peer memory.
 #include <cooperative_groups.h>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
@@ -762,11 +768,6 @@ struct PeelItem {
 constexpr int PEEL_ROWS_PER_WARP = (1 << PEEL_RP) - 32;
 constexpr int PEEL_ROWS_PER_PASS = PEEL_WARPS * PEEL_ROWS_PER_WARP;
 
-__device__ __forceinline__ uint32_t ld_stream(const uint32_t* p) {
-    uint32_t v;
-    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
-    return v;
-}
 
 struct PeelShared {
     alignas(128) uint32_t merge[PEEL_WARPS][PEEL_PM][32];
