@@ -74,12 +74,24 @@ struct Layout {
     int64_t bits_words;
 };
 
-static inline int64_t panel_words_before(int64_t l, int world, int rank) {
-    // sum_{l' < l} (l'*world + rank + 1) * TW * PW
-    return (int64_t)TW * PW * ((int64_t)world * l * (l - 1) / 2 + l * (int64_t)(rank + 1));
+// ---- geometry -------------------------------------------------------------------------------------
+// Panels are stored, owned and peeled in PAIRS: the two panels 2P, 2P+1 share 256-byte "super-rows"
+// [panel 2P: 32 words | panel 2P+1: 32 words] for rows 0 .. (2P+2)*TW-1.  A random gather of 256-byte
+// rows runs at full HBM bandwidth on B200 (~6.9 TB/s) where 128-byte rows top out at 4.0-4.7 TB/s
+// (profiles/r1_gather_probe.txt), and the peel is exactly such a gather.  Pair P belongs to rank
+// P mod world; local panel index l = 2*lp + h (lp = local pair, h = half).
+constexpr int PW2 = 2 * PW;          // words per super-row
+
+__host__ __device__ __forceinline__ int panel_of_local(int l, int world, int rank) {
+    return 2 * ((l >> 1) * world + rank) + (l & 1);
 }
-__device__ __forceinline__ int64_t d_panel_words_before(int64_t l, int world, int rank) {
-    return (int64_t)TW * PW * ((int64_t)world * l * (l - 1) / 2 + l * (int64_t)(rank + 1));
+__host__ __device__ __forceinline__ int64_t pair_words_before(int64_t lp, int world, int rank) {
+    // sum_{l' < lp} (2*(l'*world + rank) + 2) * TW * PW2
+    return (int64_t)TW * PW2 * ((int64_t)world * lp * (lp - 1) + 2 * lp * (int64_t)(rank + 1));
+}
+// word offset of (local panel l, row i, word 0)
+__host__ __device__ __forceinline__ int64_t bits_offset(int l, int64_t row, int world, int rank) {
+    return pair_words_before(l >> 1, world, rank) + row * PW2 + (l & 1) * PW;
 }
 
 static size_t cub_temp_bytes(int64_t n) {
@@ -98,9 +110,11 @@ static Layout make_layout(int64_t n, int m, int world, int rank) {
     L.n = n; L.m = m; L.world = world; L.rank = rank;
     L.npad = ceil_div(n > 0 ? n : 1, TW) * TW;
     L.np = (int)(L.npad / TW);
-    L.npl = (L.np - rank + world - 1) / world;
-    if (L.npl < 0) L.npl = 0;
-    L.npl_max = (L.np + world - 1) / world;
+    const int npairs = (L.np + 1) / 2;
+    int nlp = (npairs - rank + world - 1) / world;                 // pairs owned by this rank
+    if (nlp < 0) nlp = 0;
+    L.npl = 2 * nlp;                                               // local panel slots (the last may not exist)
+    L.npl_max = 2 * ((npairs + world - 1) / world);
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
     L.keys = take(sizeof(uint32_t) * (size_t)m * n);
@@ -127,10 +141,10 @@ static Layout make_layout(int64_t n, int m, int world, int rank) {
     L.cplanes = take(sizeof(uint32_t) * (size_t)L.npl_max * (L.kplanes + 1) * PW);
     L.mask = take(sizeof(uint32_t) * (size_t)L.npl_max * PW * world);
     L.items = take(sizeof(int) * 4 * (size_t)(L.npl_max + 2 * PEEL_MAX_GRID));
-    L.partials = take(sizeof(uint32_t) * (size_t)PEEL_MAX_GRID * PEEL_PM_MAX * 32);
+    L.partials = take(sizeof(uint32_t) * (size_t)PEEL_MAX_GRID * PEEL_PM_MAX * 64);
     L.pdone = take(sizeof(unsigned int) * 2 * (size_t)L.npl_max);      // arrivals, commits
     L.scal = take(sizeof(Scal));
-    L.bits_words = panel_words_before(L.npl, world, rank);
+    L.bits_words = pair_words_before(L.npl / 2, world, rank);
     L.bits = take(sizeof(uint32_t) * (size_t)L.bits_words);
     L.total = off;
     return L;
@@ -338,14 +352,21 @@ struct CountPlanes {
     uint32_t ones = 0, twos = 0, fours = 0, up[TILE_NUP] = {0, 0, 0, 0, 0};
 };
 
-// Copy one staged slab out (lane <-> word column: full 128-byte lines) and fold it into the planes.
-__device__ __forceinline__ void slab_out(const uint32_t* sl, uint32_t* gout, int lane, CountPlanes& cp) {
+// Copy one staged slab out (lane <-> word column: full 128-byte lines, one half of each 256-byte
+// super-row) and fold it into the planes.  `zero_sibling`: also clear the other half of the super-rows
+// (rows of an odd panel's own block have no bits in the even panel of the pair).
+__device__ __forceinline__ void slab_out(const uint32_t* sl, uint32_t* gout, int lane, CountPlanes& cp,
+                                         bool zero_sibling = false) {
     for (int rl = 0; rl < SLAB; rl += 8) {
         uint32_t v[8];
 #pragma unroll
         for (int t = 0; t < 8; ++t) v[t] = sl[rl + t];
 #pragma unroll
-        for (int t = 0; t < 8; ++t) gout[(int64_t)(rl + t) * PW + lane] = v[t];
+        for (int t = 0; t < 8; ++t) gout[(int64_t)(rl + t) * PW2 + lane] = v[t];
+        if (zero_sibling) {
+#pragma unroll
+            for (int t = 0; t < 8; ++t) gout[(int64_t)(rl + t) * PW2 - PW + lane] = 0u;
+        }
         uint32_t ta, tb, fa, fb, e;
         csa(ta, cp.ones, cp.ones, v[0], v[1]);
         csa(tb, cp.ones, cp.ones, v[2], v[3]);
@@ -489,7 +510,7 @@ __device__ __forceinline__ void tile_offdiag(const float* __restrict__ ucols, in
             }
         }
         __syncwarp();
-        slab_out(st + lane * (SLAB + 1), bits + d_panel_words_before(l, world, rank) + (int64_t)rs * PW, lane, cp);
+        slab_out(st + lane * (SLAB + 1), bits + bits_offset(l, rs, world, rank), lane, cp);
         __syncwarp();
     }
     __syncthreads();                                                       // every warp is done with f1s
@@ -558,7 +579,7 @@ __device__ __forceinline__ void tile_diag(const float* __restrict__ ucols, int64
             for (int q = 0; q < RB; ++q) st[wc * (SLAB + 1) + q * 32 + lane] = w[q];
         }
         __syncwarp();
-        slab_out(st + lane * (SLAB + 1), bits + d_panel_words_before(l, world, rank) + (int64_t)rs * PW, lane, cp);
+        slab_out(st + lane * (SLAB + 1), bits + bits_offset(l, rs, world, rank), lane, cp, (l & 1) != 0);
         __syncwarp();
     }
     counts_flush(cp, any_rows, lane, scount, count, l);
@@ -570,7 +591,7 @@ __global__ void __launch_bounds__(TILE_WARPS * 32)
 k_dominance_tiles(const float* __restrict__ ucols, int64_t npad, const Scal* __restrict__ scal,
                   uint32_t* __restrict__ bits, int* __restrict__ count, int world, int rank, int slabs) {
     const int l = blockIdx.y;
-    const int J = l * world + rank;
+    const int J = panel_of_local(l, world, rank);
     const int U = scal->U;
     const int col0 = J * TW;
     if (col0 >= U) return;
@@ -586,7 +607,7 @@ __global__ void __launch_bounds__(TILE_WARPS * 32)
 k_dominance_diag(const float* __restrict__ ucols, int64_t npad, const Scal* __restrict__ scal,
                  uint32_t* __restrict__ bits, int* __restrict__ count, int world, int rank, int slabs) {
     const int l = blockIdx.y;
-    const int J = l * world + rank;
+    const int J = panel_of_local(l, world, rank);
     const int U = scal->U;
     const int col0 = J * TW;
     if (col0 >= U) return;
@@ -602,7 +623,7 @@ __global__ void __launch_bounds__(TILE_WARPS * 32)
 k_dominance_tiles_generic(const float* __restrict__ ucols, int64_t npad, int m, const Scal* __restrict__ scal,
                           uint32_t* __restrict__ bits, int* __restrict__ count, int world, int rank) {
     const int l = blockIdx.y;
-    const int J = l * world + rank;
+    const int J = panel_of_local(l, world, rank);
     const int U = scal->U;
     const int col0 = J * TW;
     if (col0 >= U) return;
@@ -612,7 +633,9 @@ k_dominance_tiles_generic(const float* __restrict__ ucols, int64_t npad, int m, 
     const bool diag = row0 >= col0;
     const int k0 = diag ? 0 : 1;
     const int i = row0 + threadIdx.x;
-    uint32_t* gout = bits + d_panel_words_before(l, world, rank) + (int64_t)i * PW;
+    uint32_t* gout = bits + bits_offset(l, i, world, rank);
+    if (diag && (l & 1))                                                // sibling half of this super-row
+        for (int wc = 0; wc < PW; ++wc) gout[wc - PW] = 0u;
     for (int wc = 0; wc < PW; ++wc) {
         const int cb = col0 + wc * 32;
         uint32_t w = 0u;
@@ -636,7 +659,7 @@ __global__ void k_front_detect(int* __restrict__ count, int* __restrict__ rank_u
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;      // ncols is a multiple of 32
     if (t >= ncols) return;
     const int64_t l = t / TW;
-    const int64_t j = (l * world + rank) * TW + (t - l * TW);
+    const int64_t j = (int64_t)panel_of_local((int)l, world, rank) * TW + (t - l * TW);
     bool z = false;
     if (j < scal->U && count[t] == 0) {
         z = true;
@@ -658,7 +681,7 @@ __global__ void k_mask_to_list(const uint32_t* __restrict__ masks, int64_t mask_
     const int r = (int)(t / mask_words);
     const int64_t wl = t - (int64_t)r * mask_words;
     const int64_t l = wl / PW;
-    const int64_t base_col = (l * world + r) * TW + (wl - l * PW) * 32;
+    const int64_t base_col = (int64_t)panel_of_local((int)l, world, r) * TW + (wl - l * PW) * 32;
     int slot = atomicAdd(&scal->nf[k & 1], __popc(w));
     while (w) {
         const int b = __ffs(w) - 1;
@@ -677,7 +700,7 @@ k_front_apply(const uint32_t* __restrict__ bits, int* __restrict__ count, const 
     if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0 && any_out) *any_out = nf > 0;
     if (nf == 0) return;
     const int l = blockIdx.x;
-    const int J = l * world + rank;
+    const int J = panel_of_local(l, world, rank);
     const int U = scal->U;
     if (J * TW >= U) return;
     const int rowlimit = min((J + 1) * TW, U);
@@ -686,7 +709,7 @@ k_front_apply(const uint32_t* __restrict__ bits, int* __restrict__ count, const 
     __syncthreads();
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t* pbase = bits + d_panel_words_before(l, world, rank) + lane;
+    const uint32_t* pbase = bits + bits_offset(l, 0, world, rank) + lane;
     const int stride = gridDim.y * APPLY_WARPS;
     constexpr int NP_UP = 9;                                        // planes 8 .. 2048
     uint32_t ones = 0, twos = 0, fours = 0, up[NP_UP];
@@ -715,7 +738,7 @@ k_front_apply(const uint32_t* __restrict__ bits, int* __restrict__ count, const 
         for (int u = 0; u < 8; ++u) {
             const int t = t0 + u * stride;
             int i = (t < nf) ? flist[t] : 0x7FFFFFFF;
-            v[u] = (i < rowlimit) ? __ldg(pbase + (int64_t)i * PW) : 0u;
+            v[u] = (i < rowlimit) ? __ldg(pbase + (int64_t)i * PW2) : 0u;
         }
         uint32_t ta, tb, fa, fb, e;
         csa(ta, ones, ones, v[0], v[1]);
@@ -761,21 +784,27 @@ constexpr int PEEL_PM = PEEL_RP + PEEL_LOG_WARPS;   // merged over 8 warps: 15 p
 static_assert(PEEL_PM <= PEEL_PM_MAX, "raise PEEL_PM_MAX");
 constexpr int PEEL_MAX_STRIPES = 16;                // CTAs that may share one heavy panel
 
-// One unit of peel work: a panel, or one of `nstripes` row stripes of a heavy panel.
+// One unit of peel work: a panel PAIR (local pair index lp), or one of `nstripes` row stripes of a heavy pair.
 struct PeelItem {
-    int l, stripe, nstripes, slot;
+    int lp, stripe, nstripes, slot;
 };
 constexpr int PEEL_ROWS_PER_WARP = (1 << PEEL_RP) - 32;
 constexpr int PEEL_ROWS_PER_PASS = PEEL_WARPS * PEEL_ROWS_PER_WARP;
 
 
+constexpr int PEEL_STAGE_ROWS = 16;                 // 256-byte super-rows per gather-ring stage (4 KB)
+
 struct PeelShared {
-    alignas(128) uint32_t merge[PEEL_WARPS][PEEL_PM][32];
-    alignas(128) uint32_t ring[PEEL_WARPS][PEEL_STAGES * 32][32];   // per-warp bulk-copy gather ring
+    alignas(128) uint32_t merge[PEEL_WARPS][PEEL_PM][PW2];                          // both panels of the pair
+    alignas(128) uint32_t ring[PEEL_WARPS][PEEL_STAGES * PEEL_STAGE_ROWS][PW2];     // per-warp bulk-copy gather ring
     alignas(8) uint64_t bars[PEEL_WARPS][PEEL_STAGES];
-    uint32_t newmask[32];
+    uint32_t newmask[2][32];
     int nf;
     int cnt[8];                 // fused multi-rank peel: members published by each rank for this front
+};
+
+struct Planes {
+    uint32_t ones = 0, twos = 0, fours = 0, up[PEEL_UP] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
 };
 
 // ---- peer-visible state of the fused multi-rank peel ------------------------------------------------
@@ -908,13 +937,13 @@ __device__ __forceinline__ int world_barrier(Scal* scal, unsigned int& epoch, co
 
 // Warp 0, multi-rank: subtract, detect, retire, and write the new front members into this rank's
 // own region (the barrier pushes the region to the peers).
-__device__ __forceinline__ void peel_commit_world(uint32_t* cp, int K, const uint32_t (*delta)[32], int pm, int lane,
+__device__ __forceinline__ void peel_commit_world(uint32_t* cp, int K, const uint32_t* delta, int pm, int lane,
                                                   int J, const PeerTable& pt, int which_next, int* pub,
                                                   uint32_t* newmask_out) {
     uint32_t borrow = 0, nz = 0;
     for (int p = 0; p < K; ++p) {
         const uint32_t c = cp[p * PW + lane];
-        const uint32_t d = (p < pm) ? delta[p][lane] : 0u;
+        const uint32_t d = (p < pm) ? delta[p * PW2 + lane] : 0u;
         const uint32_t x = c ^ d;
         const uint32_t r = x ^ borrow;
         borrow = (~c & d) | (~x & borrow);
@@ -974,12 +1003,12 @@ __device__ __forceinline__ int grid_barrier(unsigned int* ctr, unsigned int& epo
 
 // Warp 0: subtract `delta` (bit-sliced, `pm` planes in shared memory; null = zero) from a panel's
 // count planes, find the columns that reached zero, retire them, publish them as the next front.
-__device__ __forceinline__ void peel_commit(uint32_t* cp, int K, const uint32_t (*delta)[32], int pm, int lane,
+__device__ __forceinline__ void peel_commit(uint32_t* cp, int K, const uint32_t* delta, int pm, int lane,
                                             int J, int* flist_next, int* nf_next, uint32_t* newmask_out) {
     uint32_t borrow = 0, nz = 0;
     for (int p = 0; p < K; ++p) {
         const uint32_t c = cp[p * PW + lane];
-        const uint32_t d = (p < pm) ? delta[p][lane] : 0u;
+        const uint32_t d = (p < pm) ? delta[p * PW2 + lane] : 0u;         // plane p of this half of the pair
         const uint32_t x = c ^ d;
         const uint32_t r = x ^ borrow;
         borrow = (~c & d) | (~x & borrow);
@@ -1013,6 +1042,9 @@ __device__ __forceinline__ void peel_commit(uint32_t* cp, int K, const uint32_t 
 }
 
 __device__ __forceinline__ void csa8(uint32_t& ones, uint32_t& twos, uint32_t& fours, uint32_t (&up)[PEEL_UP],
+                                     const uint32_t* x);
+__device__ __forceinline__ void csa8(Planes& pl, const uint32_t* x) { csa8(pl.ones, pl.twos, pl.fours, pl.up, x); }
+__device__ __forceinline__ void csa8(uint32_t& ones, uint32_t& twos, uint32_t& fours, uint32_t (&up)[PEEL_UP],
                                      const uint32_t* x) {
     uint32_t ta, tb, fa, fb, e;
     csa(ta, ones, ones, x[0], x[1]);
@@ -1038,12 +1070,13 @@ __device__ __forceinline__ void csa8(uint32_t& ones, uint32_t& twos, uint32_t& f
 // complete on an mbarrier; each warp owns PEEL_STAGES stages of 32 row slots in shared memory and
 // consumes one stage while the next is in flight.
 struct Ring {
-    uint32_t* slots;             // [PEEL_STAGES][32 rows][32 words]
+    uint32_t* slots;             // [PEEL_STAGES][PEEL_STAGE_ROWS][PW2]
     uint64_t* bars;              // [PEEL_STAGES] mbarriers
     int issued = 0, consumed = 0;
     int rows[PEEL_STAGES] = {0, 0};
     uint32_t phase = 0;          // bit s: parity to wait for on stage s
 };
+constexpr int PEEL_STAGE_WORDS = PEEL_STAGE_ROWS * PW2;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -1061,70 +1094,80 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         "r"(parity)
         : "memory");
 }
-__device__ __forceinline__ void bulk_copy_128(uint32_t* smem_dst, const uint32_t* gsrc, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 128, [%2];" ::"r"(
+__device__ __forceinline__ void bulk_copy_256(uint32_t* smem_dst, const uint32_t* gsrc, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 256, [%2];" ::"r"(
                      smem_u32(smem_dst)),
                  "l"(gsrc), "r"(smem_u32(bar))
                  : "memory");
 }
 
-__device__ __forceinline__ void ring_consume(Ring& rg, int lane, uint32_t& ones, uint32_t& twos, uint32_t& fours,
-                                             uint32_t (&up)[PEEL_UP]);
-__device__ __forceinline__ void peel_accumulate_ring(const int* list, int cnt, int goff, int wq, int totw, int lane,
-                                                     int rowlimit, const uint32_t* panel, Ring& rg, uint32_t& ones,
-                                                     uint32_t& twos, uint32_t& fours, uint32_t (&up)[PEEL_UP]);
-
-__device__ __forceinline__ void ring_consume(Ring& rg, int lane, uint32_t& ones, uint32_t& twos, uint32_t& fours,
-                                             uint32_t (&up)[PEEL_UP]) {
+// Wait for the oldest stage and fold its super-rows into the planes of both panels of the pair.
+__device__ __forceinline__ void ring_consume(Ring& rg, int lane, Planes& pa, Planes& pb) {
     const int st = rg.consumed & (PEEL_STAGES - 1);
     mbar_wait(rg.bars + st, (rg.phase >> st) & 1u);
     rg.phase ^= 1u << st;
     const int n = rg.rows[st];
-    const uint32_t* base = rg.slots + (st << 10) + lane;
+    const uint32_t* base = rg.slots + st * PEEL_STAGE_WORDS + lane;
     for (int r0 = 0; r0 < n; r0 += 8) {
-        uint32_t x[8];
+        uint32_t xa[8], xb[8];
 #pragma unroll
-        for (int r = 0; r < 8; ++r) x[r] = (r0 + r < n) ? base[(r0 + r) << 5] : 0u;
-        csa8(ones, twos, fours, up, x);
+        for (int r = 0; r < 8; ++r) {
+            const bool ok = r0 + r < n;
+            xa[r] = ok ? base[(r0 + r) * PW2] : 0u;
+            xb[r] = ok ? base[(r0 + r) * PW2 + PW] : 0u;
+        }
+        csa8(pa, xa);
+        csa8(pb, xb);
     }
     ++rg.consumed;
 }
 
 // Rows [0, cnt) of `list`: groups of 32 consecutive entries are dealt round-robin to the `totw` warps
-// working on this panel (all stripes together; this warp is number `wq`), starting with warp `goff`.
-// Only entries that have storage in this panel (i < rowlimit) are fetched.  `panel` is the panel's
-// base (row 0, word 0).
+// working on this pair (all stripes together; this warp is number `wq`), starting with warp `goff`.
+// Only entries that have storage in this pair (i < rowlimit) are fetched, 16 super-rows per stage.
+// `pair` is the pair's base (row 0, word 0).
 __device__ __forceinline__ void peel_accumulate_ring(const int* list, int cnt, int goff, int wq, int totw, int lane,
-                                                     int rowlimit, const uint32_t* panel, Ring& rg, uint32_t& ones,
-                                                     uint32_t& twos, uint32_t& fours, uint32_t (&up)[PEEL_UP]) {
+                                                     int rowlimit, const uint32_t* pair, Ring& rg, Planes& pa,
+                                                     Planes& pb) {
     int first = wq - goff;
     if (first < 0) first += totw;
     const int lo = first * 32, step = totw * 32;
     int mine = (lo + lane < cnt) ? __ldcg(list + lo + lane) : 0x7FFFFFFF;
     for (int t0 = lo; t0 < cnt; t0 += step) {
         const int nxt = (t0 + step + lane < cnt) ? __ldcg(list + t0 + step + lane) : 0x7FFFFFFF;
-        const bool q = mine < rowlimit;
-        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, q);
-        if (bal) {
-            if (rg.issued - rg.consumed == PEEL_STAGES) ring_consume(rg, lane, ones, twos, fours, up);
-            const int st = rg.issued & (PEEL_STAGES - 1);
-            const int total = __popc(bal);
-            const int slot = __popc(bal & ((1u << lane) - 1u));
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // earlier reads of this stage are done
-            if (lane == 0) mbar_expect_tx(rg.bars + st, (uint32_t)total * 128u);
-            __syncwarp();
-            if (q) bulk_copy_128(rg.slots + (st << 10) + (slot << 5), panel + (size_t)mine * PW, rg.bars + st);
-            rg.rows[st] = total;
-            ++rg.issued;
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            const bool q = (mine < rowlimit) && ((lane >> 4) == half);
+            const uint32_t bal = __ballot_sync(0xFFFFFFFFu, q);
+            if (bal) {
+                if (rg.issued - rg.consumed == PEEL_STAGES) ring_consume(rg, lane, pa, pb);
+                const int st = rg.issued & (PEEL_STAGES - 1);
+                const int total = __popc(bal);
+                const int slot = __popc(bal & ((1u << lane) - 1u));
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // earlier reads of this stage are done
+                if (lane == 0) mbar_expect_tx(rg.bars + st, (uint32_t)total * 256u);
+                __syncwarp();
+                if (q) bulk_copy_256(rg.slots + st * PEEL_STAGE_WORDS + slot * PW2, pair + (size_t)mine * PW2, rg.bars + st);
+                rg.rows[st] = total;
+                ++rg.issued;
+            }
         }
         mine = nxt;
     }
 }
 
 // Consume everything still in flight.
-__device__ __forceinline__ void ring_drain(Ring& rg, int lane, uint32_t& ones, uint32_t& twos, uint32_t& fours,
-                                           uint32_t (&up)[PEEL_UP]) {
-    while (rg.consumed < rg.issued) ring_consume(rg, lane, ones, twos, fours, up);
+__device__ __forceinline__ void ring_drain(Ring& rg, int lane, Planes& pa, Planes& pb) {
+    while (rg.consumed < rg.issued) ring_consume(rg, lane, pa, pb);
+}
+
+// Warp 0: commit one half (panel) of the pair.
+template <bool MULTI>
+__device__ __forceinline__ void pair_commit_half(uint32_t* cp, int K, const uint32_t* delta, int pm, int lane, int J,
+                                                 int* fl_next, int* nf_next, const PeerTable& pt, int which_next,
+                                                 int* pub, uint32_t* newmask_out) {
+    if constexpr (MULTI) peel_commit_world(cp, K, delta, pm, lane, J, pt, which_next, pub, newmask_out);
+    else peel_commit(cp, K, delta, pm, lane, J, fl_next, nf_next, newmask_out);
 }
 
 template <bool MULTI>
@@ -1144,15 +1187,14 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
     unsigned int epoch = 0;
     unsigned int* bar = reinterpret_cast<unsigned int*>(&scal->barrier);
 
-    // ---- init: int counts -> planes, alive mask, front 0 (stripe 0 of every panel) ----------------
+    // ---- init: int counts -> planes, alive mask, front 0 (stripe 0 of every pair) -----------------
     for (int sl = 0; sl < slots; ++sl) {
         const PeelItem it = items[(size_t)sl * G + B];
-        if (it.l < 0 || it.stripe != 0) continue;                   // CTA-uniform
-        const int l = it.l;
-        const int J = l * world + rank;
-        uint32_t* cp = planes_in_smem ? cp_smem + it.slot * cp_stride : cplanes + (size_t)l * cp_stride;
-        for (int c = threadIdx.x; c < TW; c += blockDim.x) {        // 32 consecutive columns per warp step
-            const int j = J * TW + c;
+        if (it.lp < 0 || it.stripe != 0) continue;                  // CTA-uniform
+        for (int c2 = threadIdx.x; c2 < 2 * TW; c2 += blockDim.x) {  // 32 consecutive columns per warp step
+            const int h = c2 >> 10, c = c2 & (TW - 1), l = 2 * it.lp + h;
+            const int j = panel_of_local(l, world, rank) * TW + c;
+            uint32_t* cp = planes_in_smem ? cp_smem + (2 * it.slot + h) * cp_stride : cplanes + (size_t)l * cp_stride;
             const int v = (j < U) ? count[(size_t)l * TW + c] : 0;
             for (int p = 0; p < K; ++p) {
                 const uint32_t w = __ballot_sync(0xFFFFFFFFu, (v >> p) & 1);
@@ -1162,13 +1204,17 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
             if (lane == 0) cp[K * PW + (c >> 5)] = a;
         }
         __syncthreads();
-        if (warp == 0) {
-            if constexpr (MULTI) peel_commit_world(cp, K, nullptr, 0, lane, J, pt, 0, &scal->pub3[0], sh.newmask);
-            else peel_commit(cp, K, nullptr, 0, lane, J, flistA, &nf3[0], sh.newmask);
+        if (warp < 2) {                                             // warp h publishes front 0 of panel h
+            const int h = warp, l = 2 * it.lp + h;
+            uint32_t* cp = planes_in_smem ? cp_smem + (2 * it.slot + h) * cp_stride : cplanes + (size_t)l * cp_stride;
+            pair_commit_half<MULTI>(cp, K, nullptr, 0, lane, panel_of_local(l, world, rank), flistA, &nf3[0], pt, 0,
+                                    &scal->pub3[0], sh.newmask[h]);
         }
         __syncthreads();
-        for (int c = threadIdx.x; c < TW; c += blockDim.x)
-            if ((sh.newmask[c >> 5] >> (c & 31)) & 1u) rank_u[(size_t)l * TW + c] = 0;
+        for (int c2 = threadIdx.x; c2 < 2 * TW; c2 += blockDim.x) {
+            const int h = c2 >> 10, c = c2 & (TW - 1);
+            if ((sh.newmask[h][c >> 5] >> (c & 31)) & 1u) rank_u[(size_t)(2 * it.lp + h) * TW + c] = 0;
+        }
         __syncthreads();
     }
     int nf = MULTI ? world_barrier(scal, epoch, pt, &scal->pub3[0], 0, sh.cnt, &sh.nf)
@@ -1195,13 +1241,12 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
         int* fl_next = (k & 1) ? flistA : flistB;
         for (int sl = 0; sl < slots; ++sl) {
             const PeelItem it = items[(size_t)sl * G + B];
-            if (it.l < 0) continue;                                   // CTA-uniform
-            const int l = it.l;
-            const int J = l * world + rank;
-            if (J * TW >= U) continue;
-            const int rowlimit = min((J + 1) * TW, U);
-            const uint32_t* pbase = bits + d_panel_words_before(l, world, rank);
-            uint32_t* cp = planes_in_smem ? cp_smem + it.slot * cp_stride : cplanes + (size_t)l * cp_stride;
+            if (it.lp < 0) continue;                                  // CTA-uniform
+            const int l0 = 2 * it.lp;
+            const int J0 = panel_of_local(l0, world, rank);           // J1 = J0 + 1
+            if (J0 * TW >= U) continue;
+            const int rowlimit = min((J0 + 2) * TW, U);               // rows stored for the pair
+            const uint32_t* pbase = bits + pair_words_before(it.lp, world, rank);
             // stripes actually used for this front: at least 512 list entries each (a short front is
             // cheaper in one CTA than spread over many and merged)
             const int ns = min(it.nstripes, max(1, nf >> 9));
@@ -1213,13 +1258,11 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
             const int pass_cap = ns * (PEEL_ROWS_PER_PASS - 32 * MAX_WORLD);
             int pr = 0, poff = 0;                                    // multi-rank: next region / offset
             for (int pass0 = 0; pass0 < nf;) {
-                uint32_t ones = 0, twos = 0, fours = 0, up[PEEL_UP];
-#pragma unroll
-                for (int p = 0; p < PEEL_UP; ++p) up[p] = 0;
+                Planes pa, pb;
                 int pass_n = 0;
                 if constexpr (!MULTI) {
                     pass_n = min(nf - pass0, pass_cap);
-                    peel_accumulate_ring(fl + pass0, pass_n, 0, wq, totw, lane, rowlimit, pbase, rg, ones, twos, fours, up);
+                    peel_accumulate_ring(fl + pass0, pass_n, 0, wq, totw, lane, rowlimit, pbase, rg, pa, pb);
                 } else {
                     int budget = pass_cap, goff = 0;
                     while (pr < pt.world && budget > 0) {
@@ -1227,12 +1270,12 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
                         if (avail <= 0) { ++pr; poff = 0; continue; }
                         const int take = min(avail, budget);
                         peel_accumulate_ring(peer_region(pt, pt.rank, k & 1, pr) + poff, take, goff, wq, totw, lane,
-                                             rowlimit, pbase, rg, ones, twos, fours, up);
+                                             rowlimit, pbase, rg, pa, pb);
                         goff = (goff + ((take + 31) >> 5)) % totw;
                         budget -= take; pass_n += take; poff += take;
                     }
                 }
-                ring_drain(rg, lane, ones, twos, fours, up);
+                ring_drain(rg, lane, pa, pb);
                 pass0 += pass_n;
                 const int groups = ((pass_n + 31) >> 5) + (MULTI ? MAX_WORLD : 0);
                 const int per = ((groups + totw - 1) / totw) << 5;    // rows a warp can have seen
@@ -1243,24 +1286,25 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
                 int pm = pmw;                                        // ... and after merging the stripes
                 if (ns > 1) { int e = 1; while ((1 << e) < ns) ++e; pm = min(pmw + e, PEEL_PM); }
                 // per-warp planes -> shared memory (only the planes that can be non-zero)
-                sh.merge[warp][0][lane] = ones;
-                sh.merge[warp][1][lane] = twos;
-                sh.merge[warp][2][lane] = fours;
+                sh.merge[warp][0][lane] = pa.ones;   sh.merge[warp][0][PW + lane] = pb.ones;
+                sh.merge[warp][1][lane] = pa.twos;   sh.merge[warp][1][PW + lane] = pb.twos;
+                sh.merge[warp][2][lane] = pa.fours;  sh.merge[warp][2][PW + lane] = pb.fours;
 #pragma unroll
                 for (int p = 0; p < PEEL_UP; ++p)
-                    if (3 + p < pm) sh.merge[warp][3 + p][lane] = up[p];
-                for (int p = PEEL_RP; p < pm; ++p) sh.merge[warp][p][lane] = 0u;
+                    if (3 + p < pm) { sh.merge[warp][3 + p][lane] = pa.up[p]; sh.merge[warp][3 + p][PW + lane] = pb.up[p]; }
+                for (int p = PEEL_RP; p < pm; ++p) { sh.merge[warp][p][lane] = 0u; sh.merge[warp][p][PW + lane] = 0u; }
                 __syncthreads();
                 if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_acc += t - t_mark; t_mark = t; }
-                // bit-sliced tree merge: warp w += warp w + half
+                // bit-sliced tree merge: warp w += warp w + half (each lane: one word of each panel)
                 for (int half = PEEL_WARPS / 2; half >= 1; half >>= 1) {
-                    if (warp < half) {
+                    if (warp < 2 * half) {                            // warps [0, half): panel 0, [half, 2 half): panel 1
+                        const int wl = warp % half, off = (warp / half) * PW + lane;
                         uint32_t carry = 0;
                         for (int p = 0; p < pm; ++p) {
-                            const uint32_t a = sh.merge[warp][p][lane], b = sh.merge[warp + half][p][lane];
-                            const uint32_t x = a ^ b;
-                            sh.merge[warp][p][lane] = x ^ carry;
-                            carry = (a & b) | (x & carry);
+                            const uint32_t a = sh.merge[wl][p][off], b2 = sh.merge[wl + half][p][off];
+                            const uint32_t x = a ^ b2;
+                            sh.merge[wl][p][off] = x ^ carry;
+                            carry = (a & b2) | (x & carry);
                         }
                     }
                     __syncthreads();
@@ -1268,37 +1312,37 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
                 bool commit = true;
                 unsigned int commits_before = 0;
                 if (ns > 1) {
-                    // Heavy panel shared by several CTAs: park this stripe's partial sum in global
+                    // Heavy pair shared by several CTAs: park this stripe's partial sums in global
                     // memory; whichever stripe arrives last adds the others to its own and commits.
-                    uint32_t* mine = partials + ((size_t)B * PEEL_PM_MAX) * 32;
-                    if (warp == 0)
-                        for (int p = 0; p < pm; ++p) __stcg(mine + p * 32 + lane, sh.merge[0][p][lane]);
+                    uint32_t* mine = partials + ((size_t)B * PEEL_PM_MAX) * PW2;
+                    if (warp < 2)
+                        for (int p = 0; p < pm; ++p) __stcg(mine + p * PW2 + warp * PW + lane, sh.merge[0][p][warp * PW + lane]);
                     __syncthreads();
                     if (threadIdx.x == 0) {
-                        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(commits_before) : "l"(&pcommit[l]) : "memory");
+                        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(commits_before) : "l"(&pcommit[it.lp]) : "memory");
                         __threadfence();
-                        const unsigned int old = atomicAdd(&pdone[l], 1u);
+                        const unsigned int old = atomicAdd(&pdone[it.lp], 1u);
                         const bool last = old + 1u == (unsigned int)ns;
-                        if (last) pdone[l] = 0u;                      // nobody touches it again before the next pass
+                        if (last) pdone[it.lp] = 0u;                  // nobody touches it again before the next pass
                         sh.nf = last ? 1 : 0;
                         __threadfence();
                     }
                     __syncthreads();
                     commit = sh.nf != 0;
-                    if (commit && warp == 0) {
+                    if (commit && warp < 2) {                         // warp h merges half h
                         for (int st2 = 0; st2 < ns; ++st2) {
                             if (st2 == it.stripe) continue;
-                            const uint32_t* other = partials + ((size_t)(B - it.stripe + st2) * PEEL_PM_MAX) * 32;
+                            const uint32_t* other = partials + ((size_t)(B - it.stripe + st2) * PEEL_PM_MAX) * PW2 + warp * PW;
                             uint32_t o[PEEL_PM];                      // all planes in flight at once (L2 latency)
 #pragma unroll
-                            for (int p = 0; p < PEEL_PM; ++p) o[p] = (p < pm) ? __ldcg(other + p * 32 + lane) : 0u;
+                            for (int p = 0; p < PEEL_PM; ++p) o[p] = (p < pm) ? __ldcg(other + p * PW2 + lane) : 0u;
                             uint32_t carry = 0;
 #pragma unroll
                             for (int p = 0; p < PEEL_PM; ++p) {
                                 if (p < pm) {
-                                    const uint32_t a = sh.merge[0][p][lane];
+                                    const uint32_t a = sh.merge[0][p][warp * PW + lane];
                                     const uint32_t x = a ^ o[p];
-                                    sh.merge[0][p][lane] = x ^ carry;
+                                    sh.merge[0][p][warp * PW + lane] = x ^ carry;
                                     carry = (a & o[p]) | (x & carry);
                                 }
                             }
@@ -1307,27 +1351,33 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
                     __syncthreads();
                 }
                 if (commit) {
-                    if (warp == 0) {
-                        if constexpr (MULTI)
-                            peel_commit_world(cp, K, sh.merge[0], pm, lane, J, pt, (k + 1) & 1, &scal->pub3[(k + 1) % 3],
-                                              sh.newmask);
-                        else
-                            peel_commit(cp, K, sh.merge[0], pm, lane, J, fl_next, &nf3[(k + 1) % 3], sh.newmask);
+                    if (warp < 2) {                                   // warp h commits panel h of the pair
+                        const int h = warp, l = l0 + h, J = J0 + h;
+                        if (J * TW >= U) {
+                            sh.newmask[h][lane] = 0u;
+                        } else {
+                            uint32_t* cp = planes_in_smem ? cp_smem + (2 * it.slot + h) * cp_stride
+                                                          : cplanes + (size_t)l * cp_stride;
+                            pair_commit_half<MULTI>(cp, K, &sh.merge[0][0][h * PW], pm, lane, J, fl_next, &nf3[(k + 1) % 3],
+                                                    pt, (k + 1) & 1, &scal->pub3[(k + 1) % 3], sh.newmask[h]);
+                        }
                     }
                     __syncthreads();
-                    for (int c = threadIdx.x; c < TW; c += blockDim.x)
-                        if ((sh.newmask[c >> 5] >> (c & 31)) & 1u) rank_u[(size_t)l * TW + c] = k + 1;
+                    for (int c = threadIdx.x; c < 2 * TW; c += blockDim.x) {
+                        const int h = c >> 10, cc = c & (TW - 1);
+                        if ((sh.newmask[h][cc >> 5] >> (cc & 31)) & 1u) rank_u[(size_t)(l0 + h) * TW + cc] = k + 1;
+                    }
                 }
                 __syncthreads();
                 if (ns > 1) {
                     // A further pass of the same front may only start (and overwrite the parked
                     // partial sums) once this pass has been committed.
                     if (threadIdx.x == 0) {
-                        if (commit) { __threadfence(); atomicAdd(&pcommit[l], 1u); }
+                        if (commit) { __threadfence(); atomicAdd(&pcommit[it.lp], 1u); }
                         if (pass0 < nf) {
                             unsigned int v;
                             do {
-                                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&pcommit[l]) : "memory");
+                                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&pcommit[it.lp]) : "memory");
                             } while (v == commits_before);
                         }
                     }
@@ -1341,7 +1391,7 @@ k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ cou
         if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_bar += t - t_mark; t_mark = t; }
     }
     if (B == 0 && threadIdx.x == 0) scal->fronts = (nf < 0) ? -1 : k;
-    if (threadIdx.x == 0 && (B == 0 || B == G - 1)) {                 // CTA 0 owns the heaviest panels
+    if (threadIdx.x == 0 && (B == 0 || B == G - 1)) {                 // CTA 0 owns the heaviest pairs
         unsigned long long* d = scal->dbg + (B == 0 ? 0 : 4);
         d[0] = t_acc; d[1] = t_mc; d[2] = t_bar; d[3] = (unsigned long long)k;
     }
@@ -1354,8 +1404,8 @@ __global__ void k_write_ranks(const int* __restrict__ row2u, const int* __restri
     const int u = row2u[i];
     int r = 0;
     if (u >= 0) {
-        const int J = u / TW;
-        if (J % world == rank) r = rank_u[(int64_t)(J / world) * TW + (u - J * TW)];
+        const int J = u / TW, P = J >> 1;
+        if (P % world == rank) r = rank_u[(int64_t)(2 * (P / world) + (J & 1)) * TW + (u - J * TW)];
     }
     out[i] = r;
 }
@@ -1529,20 +1579,21 @@ static int peel_persistent(const Plan& P, cudaStream_t s, const PeerTable* peers
     EVX_REQUIRE(per_sm >= 1, EVX_ERR_CUDA, "persistent peel kernel does not fit on an SM");
     int grid = sms * per_sm;
     if (grid > PEEL_MAX_GRID) grid = PEEL_MAX_GRID;
-    const int npl = L.npl > 0 ? L.npl : 1;
+    const int nlp = L.npl / 2;                                     // local pairs
+    const int npl = nlp > 0 ? nlp : 1;
 
     // item table: items[slot * grid + cta]
     std::vector<PeelItem> items;
     int slots = 1, planes_in_smem = 0;
-    if (L.npl >= grid) {
-        slots = (int)ceil_div(L.npl, grid);
+    if (nlp >= grid) {
+        slots = (int)ceil_div(nlp, grid);
         items.assign((size_t)slots * grid, PeelItem{-1, 0, 1, 0});
-        for (int q = 0; q < L.npl; ++q) {
+        for (int q = 0; q < nlp; ++q) {
             const int slot = q / grid, r = q % grid;
             const int cta = (slot & 1) ? (grid - 1 - r) : r;
-            items[(size_t)slot * grid + cta] = PeelItem{L.npl - 1 - q, 0, 1, slot};       // heaviest first
+            items[(size_t)slot * grid + cta] = PeelItem{nlp - 1 - q, 0, 1, slot};         // heaviest first
         }
-        planes_in_smem = ((size_t)slots * cp_bytes <= 16 * 1024) ? 1 : 0;
+        planes_in_smem = ((size_t)slots * 2 * cp_bytes <= 16 * 1024) ? 1 : 0;
     } else {
         // weights ~ rows a panel can see; stripes proportional to weight, every panel at least one
         std::vector<int> st(npl, 1);
@@ -1551,7 +1602,7 @@ static int peel_persistent(const Plan& P, cudaStream_t s, const PeerTable* peers
         int used = 0;
         for (int l = 0; l < npl; ++l) {
             int v = (int)((double)grid * (l * L.world + L.rank + 1) / wsum);
-            const int by_rows = (int)ceil_div((int64_t)(l * L.world + L.rank + 1) * TW, 32768);   // >= 32k potential rows each
+            const int by_rows = (int)ceil_div((int64_t)(l * L.world + L.rank + 1) * 2 * TW, 32768);   // >= 32k potential rows each
             if (v > by_rows) v = by_rows;
             st[l] = v < 1 ? 1 : (v > PEEL_MAX_STRIPES ? PEEL_MAX_STRIPES : v);
             used += st[l];
@@ -1561,7 +1612,7 @@ static int peel_persistent(const Plan& P, cudaStream_t s, const PeerTable* peers
                 if (st[l] > 1) { --st[l]; --used; }
         }
         auto cap = [&](int l) {
-            const int by_rows = (int)ceil_div((int64_t)(l * L.world + L.rank + 1) * TW, 32768);
+            const int by_rows = (int)ceil_div((int64_t)(l * L.world + L.rank + 1) * 2 * TW, 32768);
             return by_rows < PEEL_MAX_STRIPES ? by_rows : PEEL_MAX_STRIPES;
         };
         for (int l = npl - 1; used < grid;) {                        // spare CTAs: heaviest panels first
@@ -1580,10 +1631,10 @@ static int peel_persistent(const Plan& P, cudaStream_t s, const PeerTable* peers
             for (int t = 0; t < st[l]; ++t) items[cta++] = PeelItem{l, t, st[l], 0};
         bool split = false;
         for (int l = 0; l < npl; ++l) split |= st[l] > 1;
-        planes_in_smem = (!split && cp_bytes <= 16 * 1024) ? 1 : 0;
-        if (L.npl == 0) items.assign(1, PeelItem{-1, 0, 1, 0});
+        planes_in_smem = (!split && 2 * cp_bytes <= 16 * 1024) ? 1 : 0;
+        if (nlp == 0) items.assign(1, PeelItem{-1, 0, 1, 0});
     }
-    const size_t smem = base_smem + (planes_in_smem ? (size_t)slots * cp_bytes : 0);
+    const size_t smem = base_smem + (planes_in_smem ? (size_t)slots * 2 * cp_bytes : 0);
     EVX_CUDA(cudaMemcpyAsync(P.at<PeelItem>(L.items), items.data(), sizeof(PeelItem) * items.size(),
                              cudaMemcpyHostToDevice, s));
     EVX_CUDA(cudaStreamSynchronize(s));                              // `items` is a pageable host buffer

@@ -15,16 +15,17 @@ class NumpyShard:
         self.n, self.m, self.world, self.rank = n, m, world, rank
         self.npad = -(-max(n, 1) // TW) * TW
         self.np_ = self.npad // TW
-        self.npl_max = -(-self.np_ // world)
+        npairs = (self.np_ + 1) // 2                  # panels are owned in pairs: pair P -> rank P % world
+        self.npl_max = 2 * -(-npairs // world)
         self.mask_words = self.npl_max * PW
         self.device = torch.device("cpu")
 
     def _owned(self, u):
-        return (u // TW) % self.world == self.rank
+        return ((u // TW) // 2) % self.world == self.rank
 
     def _local(self, u):                       # label -> (local word, bit)
         J = u // TW
-        l = J // self.world
+        l = 2 * ((J // 2) // self.world) + (J % 2)
         c = u - J * TW
         return l * PW + c // 32, c % 32
 
@@ -57,7 +58,7 @@ class NumpyShard:
         for r in range(self.world):
             for wl in np.nonzero(masks[r])[0]:
                 l, w = divmod(int(wl), PW)
-                J = l * self.world + r
+                J = 2 * ((l // 2) * self.world + r) + (l % 2)
                 for b in range(32):
                     if (int(masks[r, wl]) >> b) & 1:
                         front.append(J * TW + w * 32 + b)
