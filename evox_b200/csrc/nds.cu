@@ -356,11 +356,12 @@ struct CountPlanes {
 // super-row) and fold it into the planes.  `zero_sibling`: also clear the other half of the super-rows
 // (rows of an odd panel's own block have no bits in the even panel of the pair).
 __device__ __forceinline__ void slab_out(const uint32_t* sl, uint32_t* gout, int lane, CountPlanes& cp,
-                                         bool zero_sibling = false) {
+                                         bool zero_sibling = false, uint32_t skipm = 0u) {
+    const bool dead = (skipm >> lane) & 1u;            // this lane's word was skipped: all zero, never staged
     for (int rl = 0; rl < SLAB; rl += 8) {
         uint32_t v[8];
 #pragma unroll
-        for (int t = 0; t < 8; ++t) v[t] = sl[rl + t];
+        for (int t = 0; t < 8; ++t) v[t] = dead ? 0u : sl[rl + t];
 #pragma unroll
         for (int t = 0; t < 8; ++t) gout[(int64_t)(rl + t) * PW2 + lane] = v[t];
         if (zero_sibling) {
@@ -420,6 +421,7 @@ __device__ __forceinline__ void tile_offdiag(const float* __restrict__ ucols, in
     uint32_t* stage = smem + NF * TW;                                      // [TILE_WARPS][PW][SLAB+1]
     float* wmin = reinterpret_cast<float*>(stage + TILE_WARPS * PW * (SLAB + 1));   // [PW] f1 range of each word
     float* wmax = wmin + PW;
+    uint32_t* wcm = reinterpret_cast<uint32_t*>(wmax + PW);                // [PW] valid-column mask of each word
     int* scount = reinterpret_cast<int*>(smem);                            // [TW], reuses f1s once the slabs are done
 
     for (int t = threadIdx.x; t < TW; t += blockDim.x) {
@@ -429,8 +431,10 @@ __device__ __forceinline__ void tile_offdiag(const float* __restrict__ ucols, in
         for (int k = 0; k < CR; ++k) rest[t * CR + k] = ucols[(int64_t)(3 + k) * npad + col0 + t];
     }
     __syncthreads();
-    if constexpr (M >= 2) {
-        if (threadIdx.x < PW) {
+    if (threadIdx.x < PW) {
+        const int ncol = min(32, U - (col0 + (int)threadIdx.x * 32));      // valid columns in this word
+        wcm[threadIdx.x] = (ncol >= 32) ? 0xFFFFFFFFu : (ncol <= 0 ? 0u : ((1u << ncol) - 1u));
+        if constexpr (M >= 2) {
             float lo = INFINITY, hi = -INFINITY;
             for (int c = 0; c < 32; ++c) {                                  // fminf / fmaxf skip the NaN padding
                 const float v = f1s[threadIdx.x * 32 + c];
@@ -440,8 +444,8 @@ __device__ __forceinline__ void tile_offdiag(const float* __restrict__ ucols, in
             wmin[threadIdx.x] = lo;
             wmax[threadIdx.x] = hi;
         }
-        __syncthreads();
     }
+    __syncthreads();
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t* st = stage + warp * PW * (SLAB + 1);
@@ -470,25 +474,35 @@ __device__ __forceinline__ void tile_offdiag(const float* __restrict__ ucols, in
             rmax = fmaxf(rmax, __shfl_xor_sync(0xFFFFFFFFu, rmax, o));
         }
 
-        uint32_t need_full = 0u, need_rest = 0u;                            // warp-uniform word sets
-#pragma unroll 4
-        for (int wc = 0; wc < PW; ++wc) {
-            const int ncol = min(32, U - (col0 + wc * 32));                 // valid columns in this word
-            const uint32_t cmask = (ncol >= 32) ? 0xFFFFFFFFu : (ncol <= 0 ? 0u : ((1u << ncol) - 1u));
-            bool skip = ncol <= 0, f1pass = true;
+        // Phase A: classify the 32 words (warp-uniform masks).  Lane w tests word w against the slab.
+        uint32_t skipm, need_full, need_rest = 0u;
+        {
+            bool skip = wcm[lane] == 0u, f1pass = true;
             if constexpr (M >= 2) {
-                skip = skip || (rmin > wmax[wc]);                           // every row's f1 > every column's
-                f1pass = rmax <= wmin[wc];                                  // f1 passes for every pair
+                skip = skip || (rmin > wmax[lane]);                         // every row's f1 > every column's
+                f1pass = rmax <= wmin[lane];                                // f1 passes for every pair
             }
+            skipm = __ballot_sync(0xFFFFFFFFu, skip);
+            need_full = __ballot_sync(0xFFFFFFFFu, !skip && !f1pass);
+            if constexpr (CR > 0) need_rest = ~skipm & ~need_full;
+        }
+        // Phase B: f2 suffix masks of the words that are not skipped, two words (four searches) in flight.
+        for (uint32_t todo = ~skipm; todo;) {
+            const int wa = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const int wb = todo ? __ffs(todo) - 1 : wa;
+            todo &= todo - 1 & (todo ? 0xFFFFFFFFu : 0u);
+            uint32_t ma[RB], mb[RB];
 #pragma unroll
             for (int q = 0; q < RB; ++q) {
-                uint32_t m = 0u;
-                if (!skip) m = ((M >= 3) ? f2_mask(f2s + wc * 32, xf2[q]) : 0xFFFFFFFFu) & cmask;
-                st[wc * (SLAB + 1) + q * 32 + lane] = m;
+                ma[q] = (M >= 3) ? f2_mask(f2s + wa * 32, xf2[q]) : 0xFFFFFFFFu;
+                mb[q] = (M >= 3) ? f2_mask(f2s + wb * 32, xf2[q]) : 0xFFFFFFFFu;
             }
-            if (!skip) {
-                if (!f1pass) need_full |= 1u << wc;
-                else if (CR > 0) need_rest |= 1u << wc;
+            const uint32_t ca = wcm[wa], cb2 = wcm[wb];
+#pragma unroll
+            for (int q = 0; q < RB; ++q) {
+                st[wa * (SLAB + 1) + q * 32 + lane] = ma[q] & ca;
+                st[wb * (SLAB + 1) + q * 32 + lane] = mb[q] & cb2;
             }
         }
         while (need_full) {
@@ -510,7 +524,7 @@ __device__ __forceinline__ void tile_offdiag(const float* __restrict__ ucols, in
             }
         }
         __syncwarp();
-        slab_out(st + lane * (SLAB + 1), bits + bits_offset(l, rs, world, rank), lane, cp);
+        slab_out(st + lane * (SLAB + 1), bits + bits_offset(l, rs, world, rank), lane, cp, false, skipm);
         __syncwarp();
     }
     __syncthreads();                                                       // every warp is done with f1s
@@ -1423,7 +1437,7 @@ template <int M>
 static int launch_tiles(const Plan& P, cudaStream_t s) {
     const Layout& L = P.L;
     const size_t stage_words = (size_t)TILE_WARPS * PW * (SLAB + 1);
-    const size_t smem = sizeof(uint32_t) * ((size_t)(M > 1 ? M - 1 : 1) * TW + stage_words + 2 * PW);
+    const size_t smem = sizeof(uint32_t) * ((size_t)(M > 1 ? M - 1 : 1) * TW + stage_words + 3 * PW);
     const size_t smem_diag = sizeof(uint32_t) * ((size_t)M * TW + stage_words + TW);
     EVX_CUDA(cudaFuncSetAttribute(k_dominance_tiles<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     EVX_CUDA(cudaFuncSetAttribute(k_dominance_diag<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_diag));
