@@ -337,13 +337,15 @@ __device__ __forceinline__ void word_fail(const float* f1w, const float* restw, 
 
 // Columns of a word are in ascending f2: the pairs with f2_row <= f2_col form a suffix of the word.
 __device__ __forceinline__ uint32_t f2_mask(const float* c, float r) {
-    int pos = (c[15] < r) ? 16 : 0;
-    pos += (c[pos + 7] < r) ? 8 : 0;
-    pos += (c[pos + 3] < r) ? 4 : 0;
-    pos += (c[pos + 1] < r) ? 2 : 0;
-    pos += (c[pos] < r) ? 1 : 0;
-    if (pos == 31 && c[31] < r) pos = 32;
-    return pos >= 32 ? 0u : (0xFFFFFFFFu << pos);
+    const bool none = c[31] < r;                      // off the dependent chain: even the largest f2 is below the row's
+    const float* p = c;                               // lower bound among c[0..30] by pointer walk (5 steps)
+    p += (p[15] < r) ? 16 : 0;
+    p += (p[7] < r) ? 8 : 0;
+    p += (p[3] < r) ? 4 : 0;
+    p += (p[1] < r) ? 2 : 0;
+    p += (p[0] < r) ? 1 : 0;
+    const int pos = (int)(p - c);                     // columns with f2 < r among the first 31
+    return none ? 0u : (0xFFFFFFFFu << pos);
 }
 
 constexpr int TILE_NUP = 5;                            // count planes 8 .. 128 (MAX_SLABS * SLAB = 128 rows)
