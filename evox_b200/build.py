@@ -10,7 +10,7 @@ CSRC = HERE / "csrc"
 OUT = HERE / "libevoxmo.so"
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-         "-Xcompiler", "-fPIC", "-diag-suppress", "177"]
+         "-Xcompiler", "-fPIC", "-diag-suppress", "177"] + os.environ.get("EVX_NVCC_EXTRA", "").split()
 
 
 def _stale(obj, deps):

@@ -166,6 +166,21 @@ def test_nds_full_size_properties(E, n, m):
     assert (E.operators.non_dominated_sort(x) == rank).all()                   # idempotent / deterministic
 
 
+def test_nds_heavy_fronts(E):
+    """Three stacked copies of a non-dominated layer: every front has n/3 members and every column of
+    the next layer loses n/3 dominators at once, so the peel's per-CTA share of a front exceeds what
+    the register count planes hold (several accumulate passes) and most pairs are shared by CTAs."""
+    n = 300_000
+    g = torch.Generator(device="cuda").manual_seed(5)
+    base = torch.rand((n, 3), device="cuda", generator=g)
+    base = base / base.sum(1, keepdim=True)
+    layer = (torch.arange(n, device="cuda") % 3).to(torch.float32)
+    x = base + layer[:, None]
+    rank = E.operators.non_dominated_sort(x)
+    assert (rank == layer.to(torch.int32)).all()
+    _verify_ranks_sampled(x, rank, torch.randperm(n, device="cuda", generator=g)[:256])
+
+
 # ------------------------------------------------------------------------------------------------
 # dominate_relation and the dense-matrix peel
 # ------------------------------------------------------------------------------------------------
