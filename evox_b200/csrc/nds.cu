@@ -338,16 +338,25 @@ __device__ __forceinline__ void word_fail(const float* f1w, const float* restw, 
 }
 
 // Columns of a word are in ascending f2: the pairs with f2_row <= f2_col form a suffix of the word.
-__device__ __forceinline__ uint32_t f2_mask(const float* c, float r) {
-    const bool none = c[31] < r;                      // off the dependent chain: even the largest f2 is below the row's
-    const float* p = c;                               // lower bound among c[0..30] by pointer walk (5 steps)
-    p += (p[15] < r) ? 16 : 0;
-    p += (p[7] < r) ? 8 : 0;
-    p += (p[3] < r) ? 4 : 0;
-    p += (p[1] < r) ? 2 : 0;
-    p += (p[0] < r) ? 1 : 0;
-    const int pos = (int)(p - c);                     // columns with f2 < r among the first 31
-    return none ? 0u : (0xFFFFFFFFu << pos);
+// Lower bound among the first 31 columns by walking a shared-memory BYTE address (load, compare,
+// predicated add: three instructions per step - the compiler's version kept an element index and
+// rebuilt the address every step); the compare with the largest column is off the dependent chain.
+// `caddr` must be a multiple of 128.
+__device__ __forceinline__ uint32_t f2_mask(uint32_t caddr, float r) {
+    uint32_t a = caddr, none;
+    asm("{\n\t.reg .pred p, q;\n\t.reg .f32 v, t;\n\t"
+        "ld.shared.f32 t, [%2+124];\n\t"
+        "ld.shared.f32 v, [%0+60];\n\tsetp.lt.f32 p, v, %3;\n\t@p add.u32 %0, %0, 64;\n\t"
+        "ld.shared.f32 v, [%0+28];\n\tsetp.lt.f32 p, v, %3;\n\t@p add.u32 %0, %0, 32;\n\t"
+        "ld.shared.f32 v, [%0+12];\n\tsetp.lt.f32 p, v, %3;\n\t@p add.u32 %0, %0, 16;\n\t"
+        "ld.shared.f32 v, [%0+4];\n\tsetp.lt.f32 p, v, %3;\n\t@p add.u32 %0, %0, 8;\n\t"
+        "ld.shared.f32 v, [%0];\n\tsetp.lt.f32 p, v, %3;\n\t@p add.u32 %0, %0, 4;\n\t"
+        "setp.lt.f32 q, t, %3;\n\tselp.u32 %1, 1, 0, q;\n\t}"
+        : "+r"(a), "=r"(none)
+        : "r"(caddr), "f"(r));
+    // columns with f2 < r among the first 31 = (a - caddr) / 4 = (a / 4) mod 32: the word's values
+    // start on a 128-byte boundary, and the funnel shift takes its count mod 32
+    return none ? 0u : __funnelshift_l(0u, 0xFFFFFFFFu, a >> 2);
 }
 
 constexpr int TILE_NUP = 5;                            // count planes 8 .. 128 (MAX_SLABS * SLAB = 128 rows)
@@ -385,23 +394,42 @@ __device__ __forceinline__ void slab_out(const uint32_t* sl, uint32_t* gout, int
     }
 }
 
-// Planes -> per-column integers in shared memory -> one global atomic per non-zero column.
-__device__ __forceinline__ void counts_flush(const CountPlanes& cp, bool any_rows, int lane, int* scount,
+// Column counts of the CTA's tile: the eight warps' planes are added bit-sliced in shared memory
+// (three rounds, a plane more each round), and only the sum is turned into integers - one global
+// atomic per non-zero column.  `pl` is scratch of TILE_WARPS * FLUSH_PLANES * 32 words that no warp
+// uses any more (the caller has synchronised).
+constexpr int FLUSH_PLANES = 3 + TILE_NUP + 3;         // 8 warps x 128 rows: counts up to 1024
+__device__ __forceinline__ void counts_flush(const CountPlanes& cp, int lane, int warp, uint32_t* pl,
                                              int* __restrict__ count, int l) {
-    if (any_rows) {
-#pragma unroll 4
-        for (int bb = 0; bb < 32; ++bb) {
-            const int bit = (bb + lane) & 31;
-            int v = ((cp.ones >> bit) & 1) | (((cp.twos >> bit) & 1) << 1) | (((cp.fours >> bit) & 1) << 2);
+    uint32_t* mine = pl + warp * FLUSH_PLANES * 32 + lane;
+    mine[0] = cp.ones; mine[32] = cp.twos; mine[64] = cp.fours;
 #pragma unroll
-            for (int p = 0; p < TILE_NUP; ++p) v |= ((cp.up[p] >> bit) & 1) << (3 + p);
-            if (v) atomicAdd(&scount[lane * 32 + bit], v);
-        }
-    }
+    for (int p = 0; p < TILE_NUP; ++p) mine[(3 + p) * 32] = cp.up[p];
+#pragma unroll
+    for (int p = 3 + TILE_NUP; p < FLUSH_PLANES; ++p) mine[p * 32] = 0u;
     __syncthreads();
-    for (int t = threadIdx.x; t < TW; t += blockDim.x) {
-        const int v = scount[t];
-        if (v) atomicAdd(&count[(int64_t)l * TW + t], v);
+#pragma unroll
+    for (int half = TILE_WARPS / 2; half >= 1; half >>= 1) {
+        if (warp < half) {
+            const uint32_t* other = mine + half * FLUSH_PLANES * 32;
+            uint32_t carry = 0;
+#pragma unroll
+            for (int p = 0; p < FLUSH_PLANES; ++p) {
+                const uint32_t a = mine[p * 32], b = other[p * 32];
+                const uint32_t x = a ^ b;
+                mine[p * 32] = x ^ carry;
+                carry = (a & b) | (x & carry);
+            }
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < PW / TILE_WARPS; ++i) {              // warp w: words w, w + 8, ...; lane <-> column in the word
+        const int wd = warp + TILE_WARPS * i;
+        int v = 0;
+#pragma unroll
+        for (int p = 0; p < FLUSH_PLANES; ++p) v |= (int)((pl[p * 32 + wd] >> lane) & 1u) << p;
+        if (v) atomicAdd(&count[(int64_t)l * TW + wd * 32 + lane], v);
     }
 }
 
@@ -426,7 +454,6 @@ __device__ __forceinline__ void tile_offdiag(const float* __restrict__ ucols, in
     float* wmin = reinterpret_cast<float*>(stage + TILE_WARPS * PW * (SLAB + 1));   // [PW] f1 range of each word
     float* wmax = wmin + PW;
     uint32_t* wcm = reinterpret_cast<uint32_t*>(wmax + PW);                // [PW] valid-column mask of each word
-    int* scount = reinterpret_cast<int*>(smem);                            // [TW], reuses f1s once the slabs are done
 
     for (int t = threadIdx.x; t < TW; t += blockDim.x) {
         if constexpr (M >= 2) f1s[t] = ucols[npad + col0 + t];
@@ -453,13 +480,12 @@ __device__ __forceinline__ void tile_offdiag(const float* __restrict__ ucols, in
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t* st = stage + warp * PW * (SLAB + 1);
+    const uint32_t f2addr = (uint32_t)__cvta_generic_to_shared(f2s);
     CountPlanes cp;
-    bool any_rows = false;
 
     for (int sidx = 0; sidx < slabs; ++sidx) {
         const int rs = row0 + (sidx * TILE_WARPS + warp) * SLAB;            // first row of this slab
         if (rs >= rowlimit) break;                                          // warp-uniform
-        any_rows = true;
         float xf1[RB], xf2[RB], xr[RB][CR > 0 ? CR : 1];
 #pragma unroll
         for (int q = 0; q < RB; ++q) {
@@ -499,8 +525,8 @@ __device__ __forceinline__ void tile_offdiag(const float* __restrict__ ucols, in
             uint32_t ma[RB], mb[RB];
 #pragma unroll
             for (int q = 0; q < RB; ++q) {
-                ma[q] = (M >= 3) ? f2_mask(f2s + wa * 32, xf2[q]) : 0xFFFFFFFFu;
-                mb[q] = (M >= 3) ? f2_mask(f2s + wb * 32, xf2[q]) : 0xFFFFFFFFu;
+                ma[q] = (M >= 3) ? f2_mask(f2addr + wa * 128, xf2[q]) : 0xFFFFFFFFu;
+                mb[q] = (M >= 3) ? f2_mask(f2addr + wb * 128, xf2[q]) : 0xFFFFFFFFu;
             }
             const uint32_t ca = wcm[wa], cb2 = wcm[wb];
 #pragma unroll
@@ -531,10 +557,8 @@ __device__ __forceinline__ void tile_offdiag(const float* __restrict__ ucols, in
         slab_out(st + lane * (SLAB + 1), bits + bits_offset(l, rs, world, rank), lane, cp, false, skipm);
         __syncwarp();
     }
-    __syncthreads();                                                       // every warp is done with f1s
-    for (int t = threadIdx.x; t < TW; t += blockDim.x) scount[t] = 0;
-    __syncthreads();
-    counts_flush(cp, any_rows, lane, scount, count, l);
+    __syncthreads();                                                       // every warp is done with its stage
+    counts_flush(cp, lane, warp, stage, count, l);
 }
 
 // ---- diagonal CTA: a block against its own panel ---------------------------------------------------
@@ -546,22 +570,18 @@ __device__ __forceinline__ void tile_diag(const float* __restrict__ ucols, int64
                                           int* __restrict__ count, int world, int rank, uint32_t* smem) {
     float* colv = reinterpret_cast<float*>(smem);                          // [TW][M]
     uint32_t* stage = smem + M * TW;
-    int* scount = reinterpret_cast<int*>(stage + TILE_WARPS * PW * (SLAB + 1));
     for (int t = threadIdx.x; t < M * TW; t += blockDim.x) {
         const int c = t / M, k = t - c * M;
         colv[t] = ucols[(int64_t)k * npad + col0 + c];
     }
-    for (int t = threadIdx.x; t < TW; t += blockDim.x) scount[t] = 0;
     __syncthreads();
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t* st = stage + warp * PW * (SLAB + 1);
     CountPlanes cp;
-    bool any_rows = false;
     for (int sidx = 0; sidx < slabs; ++sidx) {
         const int rs = row0 + (sidx * TILE_WARPS + warp) * SLAB;
         if (rs >= rowlimit) break;
-        any_rows = true;
         float xi[RB][M];
 #pragma unroll
         for (int q = 0; q < RB; ++q)
@@ -600,7 +620,8 @@ __device__ __forceinline__ void tile_diag(const float* __restrict__ ucols, int64
         slab_out(st + lane * (SLAB + 1), bits + bits_offset(l, rs, world, rank), lane, cp, (l & 1) != 0);
         __syncwarp();
     }
-    counts_flush(cp, any_rows, lane, scount, count, l);
+    __syncthreads();
+    counts_flush(cp, lane, warp, stage, count, l);
 }
 
 // Off-diagonal tiles: grid = (row chunks, owned panels); chunks at or past the panel's own block leave.
@@ -615,7 +636,7 @@ k_dominance_tiles(const float* __restrict__ ucols, int64_t npad, const Scal* __r
     if (col0 >= U) return;
     const int row0 = blockIdx.x * (slabs * TILE_WARPS * SLAB);
     if (row0 >= col0) return;
-    extern __shared__ __align__(16) uint32_t smem[];
+    extern __shared__ __align__(128) uint32_t smem[];
     tile_offdiag<M>(ucols, npad, U, l, col0, row0, col0, slabs, bits, count, world, rank, smem);
 }
 
@@ -632,7 +653,7 @@ k_dominance_diag(const float* __restrict__ ucols, int64_t npad, const Scal* __re
     const int rowlimit = min((J + 1) * TW, U);
     const int row0 = col0 + blockIdx.x * (slabs * TILE_WARPS * SLAB);
     if (row0 >= rowlimit) return;
-    extern __shared__ __align__(16) uint32_t smem[];
+    extern __shared__ __align__(128) uint32_t smem[];
     tile_diag<M>(ucols, npad, U, l, col0, row0, rowlimit, slabs, bits, count, world, rank, smem);
 }
 
