@@ -1459,36 +1459,15 @@ __device__ __forceinline__ void grid_barrier_plain(unsigned int* ctr, unsigned i
     __syncthreads();
     ++epoch;
     if (threadIdx.x == 0) {
-        __threadfence();
-        atomicAdd(ctr, 1u);
+        // release-add (publishes what the CTA wrote before the __syncthreads), relaxed polling, one acquire fence
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
         const unsigned int target = epoch * gridDim.x;
         unsigned int v;
         do {
             asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
         } while (v < target);
-        __threadfence();
+        asm volatile("fence.acq_rel.gpu;" ::: "memory");
     }
-    __syncthreads();
-}
-
-// In-place inclusive prefix sum of a[0..n) in shared memory by the whole CTA (256 threads).
-__device__ __forceinline__ void block_prefix(int* a, int n, int* wsum) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int per = (n + PEEL_WARPS * 32 - 1) / (PEEL_WARPS * 32);
-    const int lo = threadIdx.x * per, hi = min(lo + per, n);
-    int sum = 0;
-    for (int i = lo; i < hi; ++i) sum += a[i];
-    int incl = sum;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-        if (lane >= o) incl += t;
-    }
-    if (lane == 31) wsum[warp] = incl;
-    __syncthreads();
-    int run = incl - sum;
-    for (int w = 0; w < warp; ++w) run += wsum[w];
-    for (int i = lo; i < hi; ++i) { run += a[i]; a[i] = run; }
     __syncthreads();
 }
 
@@ -1636,6 +1615,7 @@ struct SmemDelta {                                            // planes in share
     const uint32_t* base;                                     // already offset to this lane's word
     __device__ __forceinline__ uint32_t operator()(int p) const { return base[p * PW2]; }
 };
+constexpr int DYN_MAX_PPT = 4;              // pairs per thread in the per-front scan: up to 1024 pairs (N <= 2M)
 constexpr int PEEL_WARP_PAIR_GROUPS = 4;    // a pair with at most this many groups for a front is done by one warp alone
 // Fixed cost of visiting a pair, in units of one group's gather time (~0.4 us for a CTA): a pair done by
 // one warp costs its CTA about one unit (eight of them run side by side), a pair done by the whole CTA
@@ -1652,7 +1632,7 @@ struct DynShared {
     alignas(128) uint32_t acc[PEEL_KMAX][PW2];                // this CTA's sums for the pair (all passes)
     alignas(128) uint32_t ring[PEEL_WARPS][DYN_STAGES * DYN_STAGE_ROWS][PW2];   // per-warp cp.async gather ring
     int nf;
-    int cnt[8];
+    int cnt[8], cnt2[8];
 };
 
 // A warp's register planes -> its shared-memory region, planes [0, pm).  Lane l: word l of panel 0 (pa) and of panel 1 (pb).
@@ -1718,20 +1698,64 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
         int* cnt_next = pcnt + (size_t)((k + 1) % 3) * pstride;
         int* cnt_clear = pcnt + (size_t)((k + 2) % 3) * pstride;
         for (int i = B * blockDim.x + threadIdx.x; i < npan; i += G * blockDim.x) cnt_clear[i] = 0;
-        if (threadIdx.x == 0) pre[0] = 0;
-        for (int i = threadIdx.x; i < npan; i += blockDim.x) pre[1 + i] = __ldcg(cnt + i);
-        __syncthreads();
-        block_prefix(pre + 1, npan, sh.cnt);
+        // One pass: thread t owns the pairs [t*ppt, (t+1)*ppt) - their panel counts in registers, one L2 round
+        // trip - and two block scans (members, then cost units) share three CTA-wide barriers.
+        {
+            const int ppt = (nq + PEEL_WARPS * 32 - 1) / (PEEL_WARPS * 32);     // <= DYN_MAX_PPT (host checks)
+            const int q0 = threadIdx.x * ppt;
+            int c[2 * DYN_MAX_PPT], cost[DYN_MAX_PPT];
+            int psum = 0;
+#pragma unroll
+            for (int i = 0; i < 2 * DYN_MAX_PPT; ++i) {
+                const int J = 2 * q0 + i;
+                c[i] = (i < 2 * ppt && J < npan) ? __ldcg(cnt + J) : 0;
+                psum += c[i];
+            }
+            int incl = psum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+                if (lane >= o) incl += t;
+            }
+            if (lane == 31) sh.cnt[warp] = incl;
+            __syncthreads();
+            int run = incl - psum;
+            for (int w = 0; w < warp; ++w) run += sh.cnt[w];
+            if (threadIdx.x == 0) { pre[0] = 0; S[0] = 0; }
+            int csum = 0;
+#pragma unroll
+            for (int j = 0; j < DYN_MAX_PPT; ++j) {
+                const int q = q0 + j;
+                cost[j] = 0;
+                if (j < ppt && q < nq) {
+                    run += c[2 * j];
+                    pre[2 * q + 1] = run;                           // 2q + 1 <= npan always
+                    run += c[2 * j + 1];
+                    if (2 * q + 2 <= npan) pre[2 * q + 2] = run;
+                    const int gr = (run + 31) >> 5;                 // [fixed cost | one unit per group]
+                    cost[j] = run ? gr + (gr <= PEEL_WARP_PAIR_GROUPS ? PEEL_COST_WARP_PAIR : PEEL_COST_CTA_PAIR) : 0;
+                }
+                csum += cost[j];
+            }
+            int incl2 = csum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xFFFFFFFFu, incl2, o);
+                if (lane >= o) incl2 += t;
+            }
+            if (lane == 31) sh.cnt2[warp] = incl2;
+            __syncthreads();
+            int run2 = incl2 - csum;
+            for (int w = 0; w < warp; ++w) run2 += sh.cnt2[w];
+#pragma unroll
+            for (int j = 0; j < DYN_MAX_PPT; ++j) {
+                const int q = q0 + j;
+                if (j < ppt && q < nq) { run2 += cost[j]; S[1 + q] = run2; }
+            }
+            __syncthreads();
+        }
         const int nf = pre[npan];
         if (nf <= 0) break;
-        if (threadIdx.x == 0) S[0] = 0;
-        for (int q = threadIdx.x; q < nq; q += blockDim.x) {
-            const int r = pre[min(2 * q + 2, npan)];
-            const int gr = (r + 31) >> 5;                             // [fixed cost | one unit per group]
-            S[1 + q] = r ? gr + (gr <= PEEL_WARP_PAIR_GROUPS ? PEEL_COST_WARP_PAIR : PEEL_COST_CTA_PAIR) : 0;
-        }
-        __syncthreads();
-        block_prefix(S + 1, nq, sh.cnt);
         const long long T = S[nq];
         const int lo = (int)((long long)B * T / G), hi = (int)((long long)(B + 1) * T / G);
         const int* seg = (k & 1) ? segB : segA;
@@ -2093,13 +2117,15 @@ static int peel_persistent(const Plan& P, cudaStream_t s, const PeerTable* peers
     {
         const char* e = getenv("EVX_PEEL");
         const size_t dyn_smem = sizeof(DynShared) + sizeof(int) * (size_t)(L.np + 1 + L.np / 2 + 2);
-        if (!peers && L.world == 1 && L.kplanes <= PEEL_KMAX && dyn_smem <= 113 * 1024 && !(e && strcmp(e, "static") == 0)) {
+        if (!peers && L.world == 1 && L.kplanes <= PEEL_KMAX && dyn_smem <= 113 * 1024 && (L.np + 1) / 2 <= DYN_MAX_PPT * PEEL_WARPS * 32 && !(e && strcmp(e, "static") == 0)) {
             const void* dk = (const void*)k_peel_dynamic;
             EVX_CUDA(cudaFuncSetAttribute(dk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_smem));
             EVX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dk, PEEL_WARPS * 32, dyn_smem));
             EVX_REQUIRE(per_sm >= 1, EVX_ERR_CUDA, "load-balanced peel kernel does not fit on an SM");
             int dgrid = sms * per_sm;
             if (dgrid > PEEL_MAX_GRID) dgrid = PEEL_MAX_GRID;
+            const int useful = 16 * ((L.np + 1) / 2);               // a small population cannot feed every CTA:
+            if (dgrid > useful) dgrid = useful < 32 ? 32 : useful;  // fewer arrivals per grid barrier
             const int pstride = L.npl_max + 2;
             EVX_CUDA(cudaMemsetAsync(P.at<unsigned int>(L.pdone), 0, sizeof(unsigned int) * 2 * (size_t)L.npl_max, s));
             EVX_CUDA(cudaMemsetAsync(P.at<int>(L.pcnt), 0, sizeof(int) * 3 * (size_t)pstride, s));
