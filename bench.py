@@ -20,6 +20,11 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
+# DRAM bytes per launch at N = 1M, M = 3 from ncu (profiles/r1_final_traffic_n1m.csv): read + write
+TILE_TRAFFIC_N1M = 64.85e9
+PEEL_TRAFFIC_N1M = 63.89e9
+TRAFFIC_SOURCE = "profiles/r1_final_traffic_n1m.csv (dram__bytes_read.sum + dram__bytes_write.sum per launch)"
+GATHER_PEAK_256B = 6760.0      # GB/s, random 256-byte rows through the peel's own ring (profiles/r1_gather_probe.txt)
 METRIC = "nd_sort_pairs_per_s"
 UNIT = "pairs/s"
 
@@ -273,22 +278,25 @@ def run_ours(args):
         headline = (n == 1_000_000 and m == 3)        # the ncu DRAM counters in profiles/ are for this shape
         line["roofline"] = {"bound": "hbm", "kernel": "k_dominance_tiles", "achieved": alg_bytes / t / 1e9, "peak": hbm_peak,
                             "unit": "GB/s", "frac": alg_bytes / t / 1e9 / hbm_peak,
-                            "traffic": 65.03e9 if headline else None,
-                            "traffic_source": "profiles/r1_final_traffic_n1m.csv (dram read 2.47 GB + write 62.57 GB per launch)"
-                            if headline else None,
+                            "traffic": TILE_TRAFFIC_N1M if headline else None,
+                            "traffic_source": TRAFFIC_SOURCE if headline else None,
+                            "achieved_on_traffic": (TILE_TRAFFIC_N1M / t / 1e9) if headline else None,
                             "peak_source": peak_src, "ms_per_launch": stages["tiles"],
-                            "note": "algorithmic bytes = N^2/8 (one bit per ordered pair of the reference's N x N relation); the "
-                                    "kernel stores only the half that can be non-zero and is instruction-issue bound, not HBM "
-                                    "bound (SURVEY 8d): see compare_roofline"}
+                            "note": "algorithmic bytes = N^2/8 (one bit per ordered pair of the reference's N x N relation, "
+                                    "SURVEY 8d); the kernel stores only the block-upper-triangular half that can be non-zero "
+                                    "(traffic), and what limits it is instruction issue, not HBM: see compare_roofline and "
+                                    "profiles/"}
         tp = stages["peel"] * 1e-3
         peel_bytes = pairs / 16.0                     # every stored bit is read exactly once by the peel
-        line["peel_roofline"] = {"bound": "hbm", "kernel": "k_peel_persistent", "achieved": peel_bytes / tp / 1e9,
+        line["peel_roofline"] = {"bound": "hbm", "kernel": "k_peel_dynamic", "achieved": peel_bytes / tp / 1e9,
                                  "peak": hbm_peak, "unit": "GB/s", "frac": peel_bytes / tp / 1e9 / hbm_peak,
-                                 "traffic": 62.70e9 if headline else None, "ms_per_launch": stages["peel"],
-                                 "random_gather_peak": 4290.0,
-                                 "frac_of_random_gather_peak": peel_bytes / tp / 1e9 / 4290.0,
-                                 "note": "random 128-byte row gathers: tools/probes/gather_probe.cu measures 4.29 TB/s as the "
-                                         "ceiling of that access pattern on this GPU (profiles/r1_gather_probe.txt)"}
+                                 "traffic": PEEL_TRAFFIC_N1M if headline else None, "ms_per_launch": stages["peel"],
+                                 "random_gather_peak": GATHER_PEAK_256B,
+                                 "frac_of_random_gather_peak": peel_bytes / tp / 1e9 / GATHER_PEAK_256B,
+                                 "note": "random gather of 256-byte super-rows through a cp.async ring: "
+                                         "tools/probes/gather_probe4.cu measures 6.76 TB/s for exactly this ring and consumer "
+                                         "(profiles/r1_gather_probe.txt); the rest is per-front latency (about 230 fronts, "
+                                         "one grid barrier each)"}
         line["stages_ms"] = stages
         try:
             pr = ctypes.c_double()

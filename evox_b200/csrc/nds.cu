@@ -1627,6 +1627,97 @@ __device__ __forceinline__ int pair_fixed_cost(int total) {      // total = grou
     return total <= PEEL_WARP_PAIR_GROUPS + PEEL_COST_WARP_PAIR ? PEEL_COST_WARP_PAIR : PEEL_COST_CTA_PAIR;
 }
 
+// Barrier over all CTAs of all ranks for the load-balanced kernel, carrying the front exchange.  The
+// committers have written this rank's panels of the coming front (segments + counts) into the rank's
+// OWN copy; once every local CTA has arrived, CTA 0 copies them into every peer's copy (posted stores
+// over NVLink), fences once at system scope, sends one message per peer, waits for every peer's
+// message and releases the local CTAs.  Returns 0, or -1 after a time-out (everybody leaves).
+__device__ __forceinline__ int world_barrier_seg(Scal* scal, unsigned int& epoch, const PeerTable& pt, int* cnt_next,
+                                                 int* seg_next, int nq_local, int npan, int* flag_smem) {
+    __syncthreads();
+    ++epoch;
+    const unsigned long long t0 = global_ns();
+    unsigned long long tb = t0, tn;
+    if (threadIdx.x == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(&scal->barrier) : "memory");
+    if (blockIdx.x == 0) {
+        if (threadIdx.x == 0) {
+            unsigned int v;
+            do {                                                      // every local CTA has arrived
+                asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&scal->barrier) : "memory");
+            } while (v < epoch * gridDim.x);
+            asm volatile("fence.acq_rel.gpu;" ::: "memory");
+            tn = global_ns(); scal->bdbg[1] += tn - tb; tb = tn;
+        }
+        __syncthreads();
+        if (pt.world > 1) {
+            const char* mybase = pt.base[pt.rank];
+            const size_t coff = reinterpret_cast<const char*>(cnt_next) - mybase;
+            const size_t soff = reinterpret_cast<const char*>(seg_next) - mybase;
+            for (int t = threadIdx.x; t < 2 * nq_local; t += blockDim.x) {       // one local panel per thread
+                const int J = 2 * ((t >> 1) * pt.world + pt.rank) + (t & 1);
+                if (J >= npan) continue;
+                const int c = __ldcg(cnt_next + J);
+                if (c <= 0) continue;
+                for (int r = 0; r < pt.world; ++r) {
+                    if (r == pt.rank) continue;
+                    int* pc = reinterpret_cast<int*>(pt.base[r] + coff);
+                    int* ps = reinterpret_cast<int*>(pt.base[r] + soff) + (size_t)J * TW;
+                    for (int i = 0; i < c; ++i) ps[i] = __ldcg(seg_next + (size_t)J * TW + i);
+                    pc[J] = c;
+                }
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            PeerState* me = peer_state(pt, pt.rank);
+            bool dead = false;
+            tn = global_ns(); scal->bdbg[2] += tn - tb; tb = tn;
+            __threadfence_system();                                   // the pushes are visible before the message
+            const unsigned long long msg = (unsigned long long)epoch << 32;
+            for (int r = 0; r < pt.world; ++r)
+                asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(&peer_state(pt, r)->xmsg[pt.rank]), "l"(msg)
+                             : "memory");
+            tn = global_ns(); scal->bdbg[3] += tn - tb; tb = tn;
+            for (int r = 0; r < pt.world && !dead; ++r) {             // wait for every rank's message
+                unsigned long long m;
+                do {
+                    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(m) : "l"(&me->xmsg[r]) : "memory");
+                    if ((unsigned int)(m >> 32) >= epoch) break;
+                    int ab;
+                    asm volatile("ld.relaxed.sys.global.s32 %0, [%1];" : "=r"(ab) : "l"(&me->abort) : "memory");
+                    if (ab || global_ns() - t0 > PEER_TIMEOUT_NS) dead = true;
+                } while (!dead);
+            }
+            tn = global_ns(); scal->bdbg[4] += tn - tb; tb = tn;
+            __threadfence_system();                                   // acquire: peers' pushes are visible
+            tn = global_ns(); scal->bdbg[5] += tn - tb; tb = tn;
+            if (dead) {
+                for (int r = 0; r < pt.world; ++r)
+                    asm volatile("st.relaxed.sys.global.s32 [%0], %1;" ::"l"(&peer_state(pt, r)->abort), "r"(1) : "memory");
+            }
+            scal->xtotal = dead ? -1 : 0;
+            __threadfence();
+            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&scal->go), "r"(epoch) : "memory");
+            tn = global_ns(); scal->bdbg[6] += tn - tb; tb = tn;
+        }
+    }
+    if (threadIdx.x == 0) {
+        bool dead = false;
+        if (blockIdx.x != 0) {
+            unsigned int v;
+            do {
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&scal->go) : "memory");
+            } while (v < epoch && global_ns() - t0 < 2 * PEER_TIMEOUT_NS);
+            if (v < epoch) dead = true;
+        }
+        int total;
+        asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(total) : "l"(&scal->xtotal) : "memory");
+        *flag_smem = (dead || total < 0) ? -1 : 0;
+    }
+    __syncthreads();
+    return *flag_smem;
+}
+
 struct DynShared {
     alignas(128) uint32_t merge[PEEL_WARPS][PEEL_PM][PW2];    // per-warp count planes of the pair being merged
     alignas(128) uint32_t acc[PEEL_KMAX][PW2];                // this CTA's sums for the pair (all passes)
@@ -1646,30 +1737,36 @@ __device__ __forceinline__ void store_planes(uint32_t (*m)[PW2], const Planes& p
     for (int p = PEEL_RP; p < pm; ++p) { m[p][lane] = 0u; m[p][PW + lane] = 0u; }
 }
 
+template <bool MULTI>
 __global__ void __launch_bounds__(PEEL_WARPS * 32, 2)
 k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count, int* __restrict__ rank_u, int* segA,
                int* segB, Scal* scal, uint32_t* __restrict__ cplanes, int* pcnt, int pstride, uint32_t* partials,
-               unsigned int* pdone, int K) {
+               unsigned int* pdone, int K, int world, int rank, PeerTable pt) {
     extern __shared__ __align__(128) unsigned char peel_smem_raw[];
     DynShared& sh = *reinterpret_cast<DynShared*>(peel_smem_raw);
     uint32_t (*acc)[PW2] = sh.acc;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int G = gridDim.x, B = blockIdx.x;
     const int U = scal->U;
-    const int npan = (U + TW - 1) / TW, nq = (npan + 1) / 2;        // live panels / pairs
+    const int npan = (U + TW - 1) / TW;                             // live panels, all ranks
+    const int nqg = (npan + 1) / 2;                                 // live pairs, all ranks
+    // pairs of this rank: local pair lp is global pair lp * world + rank (one GPU: the same thing)
+    const int nq = MULTI ? max(0, (nqg - rank + world - 1) / world) : nqg;
+    auto gpair = [&](int lp) { return MULTI ? lp * world + rank : lp; };
     int* pre = reinterpret_cast<int*>(peel_smem_raw + sizeof(DynShared));   // [npan + 1]
-    int* S = pre + npan + 1;                                        // [nq + 1] cost units before pair q
+    int* S = pre + npan + 1;                                        // [nq + 1] cost units before local pair lp
     const size_t cp_stride = (size_t)(K + 1) * PW;
     unsigned int epoch = 0;
     unsigned int* bar = reinterpret_cast<unsigned int*>(&scal->barrier);
 
     // ---- init: int counts -> planes, alive mask, front 0 ------------------------------------------
-    for (int Q = B; Q < nq; Q += G) {
+    for (int lp = B; lp < nq; lp += G) {
+        const int Q = gpair(lp);
         for (int c2 = threadIdx.x; c2 < 2 * TW; c2 += blockDim.x) {
-            const int h = c2 >> 10, c = c2 & (TW - 1), J = 2 * Q + h;
+            const int h = c2 >> 10, c = c2 & (TW - 1), J = 2 * Q + h, l = 2 * lp + h;
             const int j = J * TW + c;
-            uint32_t* cp = cplanes + (size_t)J * cp_stride;
-            const int v = (j < U) ? count[(size_t)J * TW + c] : 0;
+            uint32_t* cp = cplanes + (size_t)l * cp_stride;
+            const int v = (j < U) ? count[(size_t)l * TW + c] : 0;
             for (int p = 0; p < K; ++p) {
                 const uint32_t w = __ballot_sync(0xFFFFFFFFu, (v >> p) & 1);
                 if (lane == 0) __stcg(cp + p * PW + (c >> 5), w);
@@ -1679,14 +1776,21 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
         }
         __syncthreads();
         if (warp < 2) {
-            const int J = 2 * Q + warp;
+            const int J = 2 * Q + warp, l = 2 * lp + warp;
             if (J < npan)
-                peel_commit_seg(cplanes + (size_t)J * cp_stride, K, NoDelta{}, 0, lane, J, segA, pcnt + J,
-                                rank_u + (size_t)J * TW, 0);
+                peel_commit_seg(cplanes + (size_t)l * cp_stride, K, NoDelta{}, 0, lane, J, segA, pcnt + J,
+                                rank_u + (size_t)l * TW, 0);
         }
         __syncthreads();
     }
-    grid_barrier_plain(bar, epoch);
+    if constexpr (MULTI) {
+        if (world_barrier_seg(scal, epoch, pt, pcnt, segA, nq, npan, &sh.nf) < 0) {
+            if (B == 0 && threadIdx.x == 0) scal->fronts = -1;
+            return;
+        }
+    } else {
+        grid_barrier_plain(bar, epoch);
+    }
 
     Ring2 rg;
     rg.slots = &sh.ring[warp][0][0];
@@ -1698,12 +1802,12 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
         int* cnt_next = pcnt + (size_t)((k + 1) % 3) * pstride;
         int* cnt_clear = pcnt + (size_t)((k + 2) % 3) * pstride;
         for (int i = B * blockDim.x + threadIdx.x; i < npan; i += G * blockDim.x) cnt_clear[i] = 0;
-        // One pass: thread t owns the pairs [t*ppt, (t+1)*ppt) - their panel counts in registers, one L2 round
-        // trip - and two block scans (members, then cost units) share three CTA-wide barriers.
+        // Scan 1: thread t owns the global pairs [t*ppt, (t+1)*ppt) - their panel counts in registers, one L2
+        // round trip - and writes pre[].  Scan 2: thread t owns local pairs and writes S[] (cost units).
         {
-            const int ppt = (nq + PEEL_WARPS * 32 - 1) / (PEEL_WARPS * 32);     // <= DYN_MAX_PPT (host checks)
+            const int ppt = (nqg + PEEL_WARPS * 32 - 1) / (PEEL_WARPS * 32);    // <= DYN_MAX_PPT (host checks)
             const int q0 = threadIdx.x * ppt;
-            int c[2 * DYN_MAX_PPT], cost[DYN_MAX_PPT];
+            int c[2 * DYN_MAX_PPT];
             int psum = 0;
 #pragma unroll
             for (int i = 0; i < 2 * DYN_MAX_PPT; ++i) {
@@ -1722,18 +1826,29 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
             int run = incl - psum;
             for (int w = 0; w < warp; ++w) run += sh.cnt[w];
             if (threadIdx.x == 0) { pre[0] = 0; S[0] = 0; }
-            int csum = 0;
 #pragma unroll
             for (int j = 0; j < DYN_MAX_PPT; ++j) {
                 const int q = q0 + j;
-                cost[j] = 0;
-                if (j < ppt && q < nq) {
+                if (j < ppt && q < nqg) {
                     run += c[2 * j];
                     pre[2 * q + 1] = run;                           // 2q + 1 <= npan always
                     run += c[2 * j + 1];
                     if (2 * q + 2 <= npan) pre[2 * q + 2] = run;
-                    const int gr = (run + 31) >> 5;                 // [fixed cost | one unit per group]
-                    cost[j] = run ? gr + (gr <= PEEL_WARP_PAIR_GROUPS ? PEEL_COST_WARP_PAIR : PEEL_COST_CTA_PAIR) : 0;
+                }
+            }
+            __syncthreads();
+            const int ppl = (nq + PEEL_WARPS * 32 - 1) / (PEEL_WARPS * 32);
+            const int l0 = threadIdx.x * ppl;
+            int cost[DYN_MAX_PPT];
+            int csum = 0;
+#pragma unroll
+            for (int j = 0; j < DYN_MAX_PPT; ++j) {
+                const int lp = l0 + j;
+                cost[j] = 0;
+                if (j < ppl && lp < nq) {
+                    const int r = pre[min(2 * gpair(lp) + 2, npan)];
+                    const int gr = (r + 31) >> 5;                   // [fixed cost | one unit per group]
+                    cost[j] = r ? gr + (gr <= PEEL_WARP_PAIR_GROUPS ? PEEL_COST_WARP_PAIR : PEEL_COST_CTA_PAIR) : 0;
                 }
                 csum += cost[j];
             }
@@ -1749,8 +1864,8 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
             for (int w = 0; w < warp; ++w) run2 += sh.cnt2[w];
 #pragma unroll
             for (int j = 0; j < DYN_MAX_PPT; ++j) {
-                const int q = q0 + j;
-                if (j < ppt && q < nq) { run2 += cost[j]; S[1 + q] = run2; }
+                const int lp = l0 + j;
+                if (j < ppl && lp < nq) { run2 += cost[j]; S[1 + lp] = run2; }
             }
             __syncthreads();
         }
@@ -1776,17 +1891,18 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
             }
             // ---- pairs with only a few groups that lie wholly in this range: one warp each, no CTA-wide step ----
             int ord = 0;
-            for (int Q = Qa; Q < nq && S[Q] < hi; ++Q) {
-                const int tot = S[Q + 1] - S[Q];
+            for (int lp = Qa; lp < nq && S[lp] < hi; ++lp) {
+                const int Q = gpair(lp);
+                const int tot = S[lp + 1] - S[lp];
                 if (tot <= 0 || tot > PEEL_WARP_PAIR_GROUPS + PEEL_COST_WARP_PAIR) continue;
                 const int gq = tot - PEEL_COST_WARP_PAIR;
-                const int g0 = S[Q] + PEEL_COST_WARP_PAIR;          // cost unit of its first group
+                const int g0 = S[lp] + PEEL_COST_WARP_PAIR;          // cost unit of its first group
                 if (g0 < lo || g0 + gq > hi) continue;              // shared with a neighbour: below
                 if ((ord++ & (PEEL_WARPS - 1)) != warp) continue;
                 const int npre = min(2 * Q + 2, npan);
                 const int rows = pre[npre];
                 Planes pa, pb;
-                peel_accumulate_groups(pre, npre, rows, seg, 0, gq, 0, 1, lane, bits + pair_words_before(Q, 1, 0), rg, pa, pb);
+                peel_accumulate_groups(pre, npre, rows, seg, 0, gq, 0, 1, lane, bits + pair_words_before(lp, world, rank), rg, pa, pb);
                 ring2_drain(rg, lane, pa, pb);
                 int pm = 1;
                 while ((1 << pm) <= rows) ++pm;                     // <= 8 planes: at most 128 rows
@@ -1794,21 +1910,22 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
                 __syncwarp();
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
-                    const int J = 2 * Q + h;
+                    const int J = 2 * Q + h, l = 2 * lp + h;
                     if (J < npan)
-                        peel_commit_seg(cplanes + (size_t)J * cp_stride, K, SmemDelta{&sh.merge[warp][0][h * PW + lane]}, pm,
-                                        lane, J, seg_next, cnt_next + J, rank_u + (size_t)J * TW, k + 1);
+                        peel_commit_seg(cplanes + (size_t)l * cp_stride, K, SmemDelta{&sh.merge[warp][0][h * PW + lane]}, pm,
+                                        lane, J, seg_next, cnt_next + J, rank_u + (size_t)l * TW, k + 1);
                 }
                 __syncwarp();
             }
             if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_acc += t - t_mark; t_mark = t; }
             // ---- everything else: the whole CTA per pair (or per shared part of a pair) --------------------
-            for (int Q = Qa; Q < nq && S[Q] < hi; ++Q) {
-                const int tot = S[Q + 1] - S[Q];
+            for (int lp = Qa; lp < nq && S[lp] < hi; ++lp) {
+                const int Q = gpair(lp);
+                const int tot = S[lp + 1] - S[lp];
                 if (tot <= 0) continue;
                 const int fixed = pair_fixed_cost(tot);
                 const int gq = tot - fixed;
-                const int g0 = S[Q] + fixed;
+                const int g0 = S[lp] + fixed;
                 const int ga = max(lo, g0) - g0, gb = min(hi, g0 + gq) - g0;
                 if (ga >= gb) continue;                             // only the fixed-cost units fell in this range
                 if (gq <= PEEL_WARP_PAIR_GROUPS && ga == 0 && gb == gq) continue;   // done above
@@ -1820,7 +1937,7 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
                 // CTAs some ranges are empty, and then every unit has its own CTA
                 const int bf = owner(g0), bl = owner(g0 + gq - 1);
                 const int parts = (T >= G) ? bl - bf + 1 : gq;
-                const uint32_t* pbase = bits + pair_words_before(Q, 1, 0);
+                const uint32_t* pbase = bits + pair_words_before(lp, world, rank);
 
                 constexpr int PASS_GROUPS = PEEL_WARPS * (PEEL_ROWS_PER_WARP / 32);
                 // nobody to share with and one pass: the merged planes are the pair's delta as they stand
@@ -1870,16 +1987,16 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
                 }
                 bool commit = true;
                 if (parts > 1) {
-                    // Shared pair: park this CTA's sums (slot Q + B is unique per front), count
+                    // Shared pair: park this CTA's sums (slot lp + B is unique per front), count
                     // arrivals; the last one adds the others' sums to its own and commits.
-                    uint32_t* mine = partials + (size_t)(Q + B) * PEEL_KMAX * PW2;
+                    uint32_t* mine = partials + (size_t)(lp + B) * PEEL_KMAX * PW2;
                     for (int i = threadIdx.x; i < pq * PW2; i += blockDim.x) __stcg(mine + i, acc[0][i]);
                     __syncthreads();
                     if (threadIdx.x == 0) {
                         __threadfence();
-                        const unsigned int old = atomicAdd(&pdone[Q], 1u);
+                        const unsigned int old = atomicAdd(&pdone[lp], 1u);
                         const bool last = old + 1u == (unsigned int)parts;
-                        if (last) pdone[Q] = 0u;
+                        if (last) pdone[lp] = 0u;
                         sh.nf = last ? 1 : 0;
                         __threadfence();
                     }
@@ -1890,7 +2007,7 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
                         for (int i = 0; i < parts; ++i) {
                             const int b2 = (T >= G) ? bf + i : owner(g0 + i);
                             if (b2 == B) continue;
-                            const uint32_t* other = partials + (size_t)(Q + b2) * PEEL_KMAX * PW2 + off;
+                            const uint32_t* other = partials + (size_t)(lp + b2) * PEEL_KMAX * PW2 + off;
                             uint32_t o[PEEL_KMAX];
 #pragma unroll
                             for (int p = 0; p < PEEL_KMAX; ++p) o[p] = (p < pq) ? __ldcg(other + p * PW2) : 0u;
@@ -1908,17 +2025,21 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
                     }
                 }
                 if (commit && warp < 2) {
-                    const int J = 2 * Q + warp;
+                    const int J = 2 * Q + warp, l = 2 * lp + warp;
                     if (J < npan)
-                        peel_commit_seg(cplanes + (size_t)J * cp_stride, K,
+                        peel_commit_seg(cplanes + (size_t)l * cp_stride, K,
                                         SmemDelta{direct ? &sh.merge[0][0][warp * PW + lane] : &acc[0][warp * PW + lane]},
-                                        direct ? pm_last : pq, lane, J, seg_next, cnt_next + J, rank_u + (size_t)J * TW, k + 1);
+                                        direct ? pm_last : pq, lane, J, seg_next, cnt_next + J, rank_u + (size_t)l * TW, k + 1);
                 }
                 __syncthreads();
                 if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_mc += t - t_mark; t_mark = t; }
             }
         }
-        grid_barrier_plain(bar, epoch);
+        if constexpr (MULTI) {
+            if (world_barrier_seg(scal, epoch, pt, cnt_next, seg_next, nq, npan, &sh.nf) < 0) { k = -1; break; }
+        } else {
+            grid_barrier_plain(bar, epoch);
+        }
         if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_bar += t - t_mark; t_mark = t; }
     }
     if (B == 0 && threadIdx.x == 0) scal->fronts = k;
@@ -2097,6 +2218,12 @@ static int apply(const Plan& P, int k, const uint32_t* masks, int* any_out, cuda
 // With fewer panels than CTAs the spare CTAs go to the heaviest panels as extra row stripes
 // (one SM gathers at most ~226 random 128-byte rows per microsecond, see profiles/): stripes of a
 // panel sit in consecutive CTAs and the last one to arrive merges and commits.
+// Peer-mapped buffer of the load-balanced fused peel: [PeerState | counts 3 x stride | pad | segments A | segments B]
+static int peer_cnt_stride(const Layout& L) { return L.np + 2; }
+static size_t peer_seg_offset(const Layout& L) {
+    return align_up(sizeof(PeerState) + sizeof(int) * 3 * (size_t)(L.np + 2), 256);
+}
+
 static int peel_persistent(const Plan& P, cudaStream_t s, const PeerTable* peers = nullptr) {
     const Layout& L = P.L;
     int dev = 0, sms = 0, per_sm = 0;
@@ -2116,31 +2243,47 @@ static int peel_persistent(const Plan& P, cudaStream_t s, const PeerTable* peers
     // One GPU: the load-balanced kernel, unless it cannot hold its tables (or EVX_PEEL=static asks for the other).
     {
         const char* e = getenv("EVX_PEEL");
-        const size_t dyn_smem = sizeof(DynShared) + sizeof(int) * (size_t)(L.np + 1 + L.np / 2 + 2);
-        if (!peers && L.world == 1 && L.kplanes <= PEEL_KMAX && dyn_smem <= 113 * 1024 && (L.np + 1) / 2 <= DYN_MAX_PPT * PEEL_WARPS * 32 && !(e && strcmp(e, "static") == 0)) {
-            const void* dk = (const void*)k_peel_dynamic;
+        const int npairs_g = (L.np + 1) / 2;
+        const size_t dyn_smem = sizeof(DynShared) + sizeof(int) * (size_t)(L.np + 1 + nlp + 2);
+        // Fused multi-rank peel: the fixed-ownership kernel below stays the default - with the per-front
+        // world barrier dominating, the balanced kernel measured slower on 4 GPUs (21.2 vs 18.3 ms at N = 1M,
+        // equal on 2); EVX_PEEL=balanced selects it.
+        const bool want = peers ? (e && strcmp(e, "balanced") == 0) : !(e && strcmp(e, "static") == 0);
+        if (want && L.kplanes <= PEEL_KMAX && dyn_smem <= 113 * 1024 && npairs_g <= DYN_MAX_PPT * PEEL_WARPS * 32) {
+            const void* dk = peers ? (const void*)k_peel_dynamic<true> : (const void*)k_peel_dynamic<false>;
             EVX_CUDA(cudaFuncSetAttribute(dk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_smem));
             EVX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dk, PEEL_WARPS * 32, dyn_smem));
             EVX_REQUIRE(per_sm >= 1, EVX_ERR_CUDA, "load-balanced peel kernel does not fit on an SM");
             int dgrid = sms * per_sm;
             if (dgrid > PEEL_MAX_GRID) dgrid = PEEL_MAX_GRID;
-            const int useful = 16 * ((L.np + 1) / 2);               // a small population cannot feed every CTA:
+            const int useful = 16 * (nlp > 0 ? nlp : 1);            // a small population cannot feed every CTA:
             if (dgrid > useful) dgrid = useful < 32 ? 32 : useful;  // fewer arrivals per grid barrier
-            const int pstride = L.npl_max + 2;
             EVX_CUDA(cudaMemsetAsync(P.at<unsigned int>(L.pdone), 0, sizeof(unsigned int) * 2 * (size_t)L.npl_max, s));
-            EVX_CUDA(cudaMemsetAsync(P.at<int>(L.pcnt), 0, sizeof(int) * 3 * (size_t)pstride, s));
             const uint32_t* bits = P.at<uint32_t>(L.bits);
             const int* count = P.at<int>(L.count);
             int* rank_u = P.at<int>(L.rank_u);
-            int* fa = P.at<int>(L.flist);
-            int* fb = P.at<int>(L.flist2);
             Scal* scal = P.at<Scal>(L.scal);
             uint32_t* cpl = P.at<uint32_t>(L.cplanes);
-            int* pcnt = P.at<int>(L.pcnt);
             uint32_t* partials = P.at<uint32_t>(L.partials);
             unsigned int* pdone = P.at<unsigned int>(L.pdone);
-            int K = L.kplanes, ps = pstride;
-            void* args[] = {&bits, &count, &rank_u, &fa, &fb, &scal, &cpl, &pcnt, &ps, &partials, &pdone, &K};
+            int K = L.kplanes, ps = peer_cnt_stride(L), world = L.world, rank = L.rank;
+            int *pcnt, *fa, *fb;
+            PeerTable pt{};
+            if (peers) {
+                // front segments and per-panel counts live in the peer-mapped buffer (every rank holds all panels);
+                // evx_nds_shard_peer_init has cleared the counts
+                pt = *peers;
+                char* mine = pt.base[L.rank];
+                pcnt = reinterpret_cast<int*>(mine + sizeof(PeerState));
+                fa = reinterpret_cast<int*>(mine + peer_seg_offset(L));
+                fb = fa + L.npad;
+            } else {
+                pcnt = P.at<int>(L.pcnt);
+                fa = P.at<int>(L.flist);
+                fb = P.at<int>(L.flist2);
+                EVX_CUDA(cudaMemsetAsync(pcnt, 0, sizeof(int) * 3 * (size_t)ps, s));
+            }
+            void* args[] = {&bits, &count, &rank_u, &fa, &fb, &scal, &cpl, &pcnt, &ps, &partials, &pdone, &K, &world, &rank, &pt};
             EVX_CUDA(cudaLaunchCooperativeKernel(dk, dim3(dgrid), dim3(PEEL_WARPS * 32), args, dyn_smem, s));
             ++evx::launch_counter();
             return EVX_OK;
@@ -2303,12 +2446,14 @@ extern "C" int evx_nds_shard_ranks(evx_nds_shard* p, int32_t* rank_partial, void
 extern "C" size_t evx_nds_shard_peer_bytes(const evx_nds_shard* p) {
     if (!p) return 0;
     const Layout& L = p->P.L;
-    return sizeof(PeerState) + 2 * sizeof(int) * (size_t)L.world * ((size_t)L.npl_max * TW);
+    const size_t lists = sizeof(PeerState) + 2 * sizeof(int) * (size_t)L.world * ((size_t)L.npl_max * TW);   // EVX_PEEL=static
+    const size_t segs = peer_seg_offset(L) + 2 * sizeof(int) * (size_t)L.npad;
+    return lists > segs ? lists : segs;
 }
 
 extern "C" int evx_nds_shard_peer_init(evx_nds_shard* p, void* local_peer_buf, void* stream) {
     EVX_REQUIRE(p && local_peer_buf, EVX_ERR_ARG, "evx_nds_shard_peer_init: null argument");
-    EVX_CUDA(cudaMemsetAsync(local_peer_buf, 0, sizeof(PeerState), (cudaStream_t)stream));
+    EVX_CUDA(cudaMemsetAsync(local_peer_buf, 0, peer_seg_offset(p->P.L), (cudaStream_t)stream));   // state + per-panel counts
     return EVX_OK;
 }
 

@@ -75,11 +75,15 @@ def test_stepwise_peel_env_switch(monkeypatch):
     assert torch.equal(a, b)
 
 
-def test_fused_peel_world_of_one():
+@pytest.mark.parametrize("peel", ["default", "balanced"])
+def test_fused_peel_world_of_one(peel, monkeypatch):
     """The fused multi-rank peel kernel (peer-mapped lists, world-wide barrier) with a process group of
     one rank: same kernel and protocol as on 8 GPUs, peers == self.  Multi-GPU runs are exercised by
-    tools/fused_check.py under torchrun (see profiles/r1_scaling.md)."""
+    tools/fused_check.py under torchrun (see profiles/r1_scaling.md).  `balanced` = the load-balanced
+    kernel with per-panel segments in the peer buffer (EVX_PEEL=balanced), default = fixed ownership."""
     import os
+    if peel != "default":
+        monkeypatch.setenv("EVX_PEEL", peel)
     import torch.distributed as dist
     from oracle import oracle_c as C
     from evox_b200.distributed import FusedShardedNonDominatedSort
