@@ -171,7 +171,8 @@ int evx_profile_last(float* prep_ms, float* tiles_ms, float* peel_ms);
 /* nanoseconds the persistent peel kernel of the plan's last run spent in {accumulate, merge+commit,
  * barrier, fronts} as seen by its first CTA (out16[0..3]) and its last CTA (out16[4..7]); out16[8..14]:
  * steps of the multi-rank barrier as seen by CTA 0 (own fence+arrive, local wait, fence, send, peer
- * wait, fence, release), summed over fronts.                                                       */
+ * wait, fence, release), summed over fronts.  p == NULL: the values of this host thread's last
+ * evx_nds_f32 call made with evx_profile_enable(1).                                                 */
 int evx_debug_peel_times(evx_nds_shard* p, uint64_t* out16);
 /* register-only issue-rate probe: runs `iters` dependent-free compare+logic steps per thread on
  * the whole chip and returns the measured pair-tests per second for the inner step the dominance
