@@ -32,6 +32,8 @@
 #include <cstring>
 #include <vector>
 
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace evx {
@@ -342,21 +344,23 @@ __device__ __forceinline__ void word_fail(const float* f1w, const float* restw, 
 // predicated add: three instructions per step - the compiler's version kept an element index and
 // rebuilt the address every step); the compare with the largest column is off the dependent chain.
 // `caddr` must be a multiple of 128.
-__device__ __forceinline__ uint32_t f2_mask(uint32_t caddr, float r) {
-    uint32_t a = caddr, none;
-    asm("{\n\t.reg .pred p, q;\n\t.reg .f32 v, t;\n\t"
-        "ld.shared.f32 t, [%2+124];\n\t"
-        "ld.shared.f32 v, [%0+60];\n\tsetp.lt.f32 p, v, %3;\n\t@p add.u32 %0, %0, 64;\n\t"
-        "ld.shared.f32 v, [%0+28];\n\tsetp.lt.f32 p, v, %3;\n\t@p add.u32 %0, %0, 32;\n\t"
-        "ld.shared.f32 v, [%0+12];\n\tsetp.lt.f32 p, v, %3;\n\t@p add.u32 %0, %0, 16;\n\t"
-        "ld.shared.f32 v, [%0+4];\n\tsetp.lt.f32 p, v, %3;\n\t@p add.u32 %0, %0, 8;\n\t"
-        "ld.shared.f32 v, [%0];\n\tsetp.lt.f32 p, v, %3;\n\t@p add.u32 %0, %0, 4;\n\t"
-        "setp.lt.f32 q, t, %3;\n\tselp.u32 %1, 1, 0, q;\n\t}"
-        : "+r"(a), "=r"(none)
-        : "r"(caddr), "f"(r));
+// `c15` and `c31` are the word's 16th and last value, loaded by the caller: their addresses are the
+// same for every lane and for both rows of a lane, so one load serves two searches and the first step
+// is a compare and a select.
+__device__ __forceinline__ uint32_t f2_mask(uint32_t caddr, float c15, float c31, float r) {
+    uint32_t a;
+    asm("{\n\t.reg .pred p;\n\t.reg .f32 v;\n\t"
+        "mov.u32 %0, %2;\n\t"
+        "setp.lt.f32 p, %3, %1;\n\t@p add.u32 %0, %0, 64;\n\t"
+        "ld.shared.f32 v, [%0+28];\n\tsetp.lt.f32 p, v, %1;\n\t@p add.u32 %0, %0, 32;\n\t"
+        "ld.shared.f32 v, [%0+12];\n\tsetp.lt.f32 p, v, %1;\n\t@p add.u32 %0, %0, 16;\n\t"
+        "ld.shared.f32 v, [%0+4];\n\tsetp.lt.f32 p, v, %1;\n\t@p add.u32 %0, %0, 8;\n\t"
+        "ld.shared.f32 v, [%0];\n\tsetp.lt.f32 p, v, %1;\n\t@p add.u32 %0, %0, 4;\n\t}"
+        : "=&r"(a)
+        : "f"(r), "r"(caddr), "f"(c15));
     // columns with f2 < r among the first 31 = (a - caddr) / 4 = (a / 4) mod 32: the word's values
     // start on a 128-byte boundary, and the funnel shift takes its count mod 32
-    return none ? 0u : __funnelshift_l(0u, 0xFFFFFFFFu, a >> 2);
+    return (c31 < r) ? 0u : __funnelshift_l(0u, 0xFFFFFFFFu, a >> 2);
 }
 
 constexpr int TILE_NUP = 5;                            // count planes 8 .. 128 (MAX_SLABS * SLAB = 128 rows)
@@ -517,24 +521,38 @@ __device__ __forceinline__ void tile_offdiag(const float* __restrict__ ucols, in
             if constexpr (CR > 0) need_rest = ~skipm & ~need_full;
         }
         // Phase B: f2 suffix masks of the words that are not skipped, two words (four searches) in flight.
-        for (uint32_t todo = ~skipm; todo;) {
-            const int wa = __ffs(todo) - 1;
-            todo &= todo - 1;
-            const int wb = todo ? __ffs(todo) - 1 : wa;
-            todo &= todo - 1 & (todo ? 0xFFFFFFFFu : 0u);
-            uint32_t ma[RB], mb[RB];
+        // (words are in ascending f1 inside the panel, so the skipped ones are a prefix and the live ones a
+        // range: a counted loop.  A skipped word inside the range would only cost work: slab_out ignores it.)
+        const uint32_t live = ~skipm;
+        const int wlo = live ? __ffs(live) - 1 : 0, whi = live ? 32 - __clz(live) : 0;
+        auto phase_b = [&](auto full_tag) {
+            constexpr bool FULLP = decltype(full_tag)::value;          // every column of the panel exists: no validity mask
+            for (int wa = wlo; wa < whi; wa += 2) {
+                const int wb = min(wa + 1, whi - 1);
+                uint32_t ma[RB], mb[RB];
+                if constexpr (M >= 3) {
+                    const uint32_t aa = f2addr + wa * 128, ab = f2addr + wb * 128;
+                    const float a15 = f2s[wa * 32 + 15], a31 = f2s[wa * 32 + 31];
+                    const float b15 = f2s[wb * 32 + 15], b31 = f2s[wb * 32 + 31];
 #pragma unroll
-            for (int q = 0; q < RB; ++q) {
-                ma[q] = (M >= 3) ? f2_mask(f2addr + wa * 128, xf2[q]) : 0xFFFFFFFFu;
-                mb[q] = (M >= 3) ? f2_mask(f2addr + wb * 128, xf2[q]) : 0xFFFFFFFFu;
-            }
-            const uint32_t ca = wcm[wa], cb2 = wcm[wb];
+                    for (int q = 0; q < RB; ++q) {
+                        ma[q] = f2_mask(aa, a15, a31, xf2[q]);
+                        mb[q] = f2_mask(ab, b15, b31, xf2[q]);
+                    }
+                } else {
 #pragma unroll
-            for (int q = 0; q < RB; ++q) {
-                st[wa * (SLAB + 1) + q * 32 + lane] = ma[q] & ca;
-                st[wb * (SLAB + 1) + q * 32 + lane] = mb[q] & cb2;
+                    for (int q = 0; q < RB; ++q) ma[q] = mb[q] = 0xFFFFFFFFu;
+                }
+                const uint32_t ca = FULLP ? 0xFFFFFFFFu : wcm[wa], cb2 = FULLP ? 0xFFFFFFFFu : wcm[wb];
+#pragma unroll
+                for (int q = 0; q < RB; ++q) {
+                    st[wa * (SLAB + 1) + q * 32 + lane] = ma[q] & ca;
+                    st[wb * (SLAB + 1) + q * 32 + lane] = mb[q] & cb2;
+                }
             }
-        }
+        };
+        if (col0 + TW <= U) phase_b(std::true_type{});
+        else phase_b(std::false_type{});
         while (need_full) {
             const int wc = __ffs(need_full) - 1;
             need_full &= need_full - 1;
