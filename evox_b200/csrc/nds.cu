@@ -40,10 +40,16 @@ namespace evx {
 
 constexpr int TW = 1024;            // columns per panel
 constexpr int PW = TW / 32;         // words per panel row (128 B)
-constexpr int RB = 2;               // rows per lane in the tile kernel
+#ifndef EVX_RB
+#define EVX_RB 1
+#endif
+#ifndef EVX_MAX_SLABS
+#define EVX_MAX_SLABS 4
+#endif
+constexpr int RB = EVX_RB;          // rows per lane in the tile kernel
 constexpr int TILE_WARPS = 8;
 constexpr int SLAB = 32 * RB;       // rows per warp and pass
-constexpr int MAX_SLABS = 2;        // passes per warp (count planes stay in registers across passes)
+constexpr int MAX_SLABS = EVX_MAX_SLABS;   // passes per warp (count planes stay in registers across passes)
 constexpr int APPLY_WARPS = 8;
 constexpr int SMALL_PATH_MAX_N = 1024;   // populations of at most one panel take the direct small path
 constexpr int PEEL_MAX_GRID = 1024;  // upper bound on the CTAs of the persistent peel kernel
@@ -363,10 +369,12 @@ __device__ __forceinline__ uint32_t f2_mask(uint32_t caddr, float c15, float c31
     return (c31 < r) ? 0u : __funnelshift_l(0u, 0xFFFFFFFFu, a >> 2);
 }
 
-constexpr int TILE_NUP = 5;                            // count planes 8 .. 128 (MAX_SLABS * SLAB = 128 rows)
+constexpr int tile_count_bits(int rows) { return rows <= 1 ? 1 : 1 + tile_count_bits(rows / 2); }
+constexpr int TILE_NUP = tile_count_bits(MAX_SLABS * SLAB) - 3;   // count planes 8 .. MAX_SLABS * SLAB (5 for 128 rows)
+static_assert(TW % (MAX_SLABS * TILE_WARPS * SLAB) == 0, "a CTA's rows must tile a block");
 
 struct CountPlanes {
-    uint32_t ones = 0, twos = 0, fours = 0, up[TILE_NUP] = {0, 0, 0, 0, 0};
+    uint32_t ones = 0, twos = 0, fours = 0, up[TILE_NUP] = {};
 };
 
 // Copy one staged slab out (lane <-> word column: full 128-byte lines, one half of each 256-byte
@@ -1634,12 +1642,21 @@ struct SmemDelta {                                            // planes in share
     __device__ __forceinline__ uint32_t operator()(int p) const { return base[p * PW2]; }
 };
 constexpr int DYN_MAX_PPT = 4;              // pairs per thread in the per-front scan: up to 1024 pairs (N <= 2M)
-constexpr int PEEL_WARP_PAIR_GROUPS = 4;    // a pair with at most this many groups for a front is done by one warp alone
+#ifndef EVX_WPG
+#define EVX_WPG 1
+#endif
+#ifndef EVX_CW
+#define EVX_CW 2
+#endif
+#ifndef EVX_CC
+#define EVX_CC 12
+#endif
+constexpr int PEEL_WARP_PAIR_GROUPS = EVX_WPG;    // a pair with at most this many groups for a front is done by one warp alone
 // Fixed cost of visiting a pair, in units of one group's gather time (~0.4 us for a CTA): a pair done by
 // one warp costs its CTA about one unit (eight of them run side by side), a pair done by the whole CTA
 // pays for the merge tree, the commit and four CTA-wide barriers.
-constexpr int PEEL_COST_WARP_PAIR = 2;
-constexpr int PEEL_COST_CTA_PAIR = 12;
+constexpr int PEEL_COST_WARP_PAIR = EVX_CW;
+constexpr int PEEL_COST_CTA_PAIR = EVX_CC;
 static_assert(PEEL_WARP_PAIR_GROUPS + PEEL_COST_WARP_PAIR < 1 + PEEL_COST_CTA_PAIR, "the two kinds must be told apart by total cost");
 __device__ __forceinline__ int pair_fixed_cost(int total) {      // total = groups + fixed cost (> 0)
     return total <= PEEL_WARP_PAIR_GROUPS + PEEL_COST_WARP_PAIR ? PEEL_COST_WARP_PAIR : PEEL_COST_CTA_PAIR;
