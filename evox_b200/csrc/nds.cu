@@ -40,16 +40,12 @@ namespace evx {
 
 constexpr int TW = 1024;            // columns per panel
 constexpr int PW = TW / 32;         // words per panel row (128 B)
-#ifndef EVX_RB
-#define EVX_RB 1
-#endif
-#ifndef EVX_MAX_SLABS
-#define EVX_MAX_SLABS 4
-#endif
-constexpr int RB = EVX_RB;          // rows per lane in the tile kernel
+// Rows per lane in the tile kernel.  M <= 3: one row per lane (more CTAs per SM hide the latency of the
+// f2 searches: 19.1 -> 17.7 ms at N = 1M); M > 3: two, so that every column value staged for the
+// sign-bit compares serves two rows (N = 100k, M = 10: 1.64 vs 1.78 ms).  A warp always covers 128 rows.
+__host__ __device__ constexpr int tile_rb(int m) { return m <= 3 ? 1 : 2; }
 constexpr int TILE_WARPS = 8;
-constexpr int SLAB = 32 * RB;       // rows per warp and pass
-constexpr int MAX_SLABS = EVX_MAX_SLABS;   // passes per warp (count planes stay in registers across passes)
+constexpr int TILE_ROWS_PER_WARP = 128;                 // slabs per warp = 128 / (32 * rows per lane)
 constexpr int APPLY_WARPS = 8;
 constexpr int SMALL_PATH_MAX_N = 1024;   // populations of at most one panel take the direct small path
 constexpr int PEEL_MAX_GRID = 1024;  // upper bound on the CTAs of the persistent peel kernel
@@ -299,7 +295,7 @@ __device__ __forceinline__ void load_col(const float* p, float (&v)[C]) {
 //
 // Fail bits of 32 columns x RB rows for objective f1 (if F1) and the CR objectives 3 .. M-1.
 // f1w: the word's 32 f1 values (SoA); restw: its [32][CR] remaining values.
-template <int CR, bool F1>
+template <int CR, bool F1, int RB>
 __device__ __forceinline__ void word_fail(const float* f1w, const float* restw, const float (&xf1)[RB],
                                           const float (&xr)[RB][CR > 0 ? CR : 1], uint32_t (&w)[RB]) {
 #pragma unroll
@@ -369,9 +365,7 @@ __device__ __forceinline__ uint32_t f2_mask(uint32_t caddr, float c15, float c31
     return (c31 < r) ? 0u : __funnelshift_l(0u, 0xFFFFFFFFu, a >> 2);
 }
 
-constexpr int tile_count_bits(int rows) { return rows <= 1 ? 1 : 1 + tile_count_bits(rows / 2); }
-constexpr int TILE_NUP = tile_count_bits(MAX_SLABS * SLAB) - 3;   // count planes 8 .. MAX_SLABS * SLAB (5 for 128 rows)
-static_assert(TW % (MAX_SLABS * TILE_WARPS * SLAB) == 0, "a CTA's rows must tile a block");
+constexpr int TILE_NUP = 5;                            // count planes 8 .. 128 (a warp's 128 rows)
 
 struct CountPlanes {
     uint32_t ones = 0, twos = 0, fours = 0, up[TILE_NUP] = {};
@@ -380,6 +374,7 @@ struct CountPlanes {
 // Copy one staged slab out (lane <-> word column: full 128-byte lines, one half of each 256-byte
 // super-row) and fold it into the planes.  `zero_sibling`: also clear the other half of the super-rows
 // (rows of an odd panel's own block have no bits in the even panel of the pair).
+template <int SLAB>
 __device__ __forceinline__ void slab_out(const uint32_t* sl, uint32_t* gout, int lane, CountPlanes& cp,
                                          bool zero_sibling = false, uint32_t skipm = 0u) {
     const bool dead = (skipm >> lane) & 1u;            // this lane's word was skipped: all zero, never staged
@@ -457,6 +452,7 @@ template <int M>
 __device__ __forceinline__ void tile_offdiag(const float* __restrict__ ucols, int64_t npad, int U, int l, int col0,
                                              int row0, int rowlimit, int slabs, uint32_t* __restrict__ bits,
                                              int* __restrict__ count, int world, int rank, uint32_t* smem) {
+    constexpr int RB = tile_rb(M), SLAB = 32 * RB;
     constexpr int CR = (M > 3) ? M - 3 : 0;
     constexpr int NF = (M > 1) ? M - 1 : 1;                                // staged objective arrays
     float* f1s = reinterpret_cast<float*>(smem);                           // [TW]
@@ -565,7 +561,7 @@ __device__ __forceinline__ void tile_offdiag(const float* __restrict__ ucols, in
             const int wc = __ffs(need_full) - 1;
             need_full &= need_full - 1;
             uint32_t f[RB];
-            word_fail<CR, true>(f1s + wc * 32, rest + wc * 32 * CR, xf1, xr, f);
+            word_fail<CR, true, RB>(f1s + wc * 32, rest + wc * 32 * CR, xf1, xr, f);
 #pragma unroll
             for (int q = 0; q < RB; ++q) st[wc * (SLAB + 1) + q * 32 + lane] &= ~f[q];
         }
@@ -574,13 +570,13 @@ __device__ __forceinline__ void tile_offdiag(const float* __restrict__ ucols, in
                 const int wc = __ffs(need_rest) - 1;
                 need_rest &= need_rest - 1;
                 uint32_t f[RB];
-                word_fail<CR, false>(f1s + wc * 32, rest + wc * 32 * CR, xf1, xr, f);
+                word_fail<CR, false, RB>(f1s + wc * 32, rest + wc * 32 * CR, xf1, xr, f);
 #pragma unroll
                 for (int q = 0; q < RB; ++q) st[wc * (SLAB + 1) + q * 32 + lane] &= ~f[q];
             }
         }
         __syncwarp();
-        slab_out(st + lane * (SLAB + 1), bits + bits_offset(l, rs, world, rank), lane, cp, false, skipm);
+        slab_out<SLAB>(st + lane * (SLAB + 1), bits + bits_offset(l, rs, world, rank), lane, cp, false, skipm);
         __syncwarp();
     }
     __syncthreads();                                                       // every warp is done with its stage
@@ -594,6 +590,7 @@ template <int M>
 __device__ __forceinline__ void tile_diag(const float* __restrict__ ucols, int64_t npad, int U, int l, int col0,
                                           int row0, int rowlimit, int slabs, uint32_t* __restrict__ bits,
                                           int* __restrict__ count, int world, int rank, uint32_t* smem) {
+    constexpr int RB = tile_rb(M), SLAB = 32 * RB;
     float* colv = reinterpret_cast<float*>(smem);                          // [TW][M]
     uint32_t* stage = smem + M * TW;
     for (int t = threadIdx.x; t < M * TW; t += blockDim.x) {
@@ -643,7 +640,7 @@ __device__ __forceinline__ void tile_diag(const float* __restrict__ ucols, int64
             for (int q = 0; q < RB; ++q) st[wc * (SLAB + 1) + q * 32 + lane] = w[q];
         }
         __syncwarp();
-        slab_out(st + lane * (SLAB + 1), bits + bits_offset(l, rs, world, rank), lane, cp, (l & 1) != 0);
+        slab_out<SLAB>(st + lane * (SLAB + 1), bits + bits_offset(l, rs, world, rank), lane, cp, (l & 1) != 0);
         __syncwarp();
     }
     __syncthreads();
@@ -660,7 +657,7 @@ k_dominance_tiles(const float* __restrict__ ucols, int64_t npad, const Scal* __r
     const int U = scal->U;
     const int col0 = J * TW;
     if (col0 >= U) return;
-    const int row0 = blockIdx.x * (slabs * TILE_WARPS * SLAB);
+    const int row0 = blockIdx.x * (slabs * TILE_WARPS * 32 * tile_rb(M));
     if (row0 >= col0) return;
     extern __shared__ __align__(128) uint32_t smem[];
     tile_offdiag<M>(ucols, npad, U, l, col0, row0, col0, slabs, bits, count, world, rank, smem);
@@ -677,7 +674,7 @@ k_dominance_diag(const float* __restrict__ ucols, int64_t npad, const Scal* __re
     const int col0 = J * TW;
     if (col0 >= U) return;
     const int rowlimit = min((J + 1) * TW, U);
-    const int row0 = col0 + blockIdx.x * (slabs * TILE_WARPS * SLAB);
+    const int row0 = col0 + blockIdx.x * (slabs * TILE_WARPS * 32 * tile_rb(M));
     if (row0 >= rowlimit) return;
     extern __shared__ __align__(128) uint32_t smem[];
     tile_diag<M>(ucols, npad, U, l, col0, row0, rowlimit, slabs, bits, count, world, rank, smem);
@@ -2109,6 +2106,8 @@ struct Plan {
 template <int M>
 static int launch_tiles(const Plan& P, cudaStream_t s) {
     const Layout& L = P.L;
+    constexpr int SLAB = 32 * tile_rb(M), MAX_SLABS = TILE_ROWS_PER_WARP / SLAB;
+    static_assert(TW % (MAX_SLABS * TILE_WARPS * SLAB) == 0, "a CTA's rows must tile a block");
     const size_t stage_words = (size_t)TILE_WARPS * PW * (SLAB + 1);
     const size_t smem = sizeof(uint32_t) * ((size_t)(M > 1 ? M - 1 : 1) * TW + stage_words + 3 * PW);
     const size_t smem_diag = sizeof(uint32_t) * ((size_t)M * TW + stage_words + TW);
