@@ -13,17 +13,19 @@
 //   4. For labelled rows i, j: block(i) < block(j)  =>  i dominates j  <=>  f_k[i] <= f_k[j] for all
 //      k >= 1 (f0 by the order, strictness by uniqueness); block(i) > block(j) => never; same block:
 //      all M objectives.  Only the block-upper triangle exists.
-//   5. Tiles: a 64-row slab against a 32-column word is classified by its f1 ranges (skip / f1
-//      passes / mixed); f2 is a binary-searched suffix mask; what remains is compared on the FMA
-//      pipe (sign of b - a).
-//   6. The bit matrix is stored by column PANELS of TW columns: panel J holds rows 0 .. (J+1)*TW-1,
-//      each row PW = 32 words (128 B).  Packed: N^2/16 bytes.  A panel and the dominator counts of
-//      its columns are owned by one rank (J mod world).
-//   7. Peeling: front k = columns whose count is 0.  Every front row is read exactly once per panel
-//      (one 128-byte bulk copy), rows are summed bit-sliced (carry-save adders), subtracted from
-//      bit-sliced counts, and "count == 0" is the NOR of the planes.  One persistent cooperative
-//      kernel peels all fronts; on several GPUs the same kernel also exchanges front membership over
-//      NVLink peer memory.
+//   5. Tiles: a slab of rows (32, or 64 for M > 3) against a 32-column word is classified by its f1
+//      ranges (skip / f1 passes / mixed); f2 is a binary-searched suffix mask; what remains is
+//      compared on the FMA pipe (sign of b - a).
+//   6. The bit matrix is stored by column PANELS of TW columns, two panels side by side: pair P holds
+//      rows 0 .. (2P+2)*TW-1 as 256-byte super-rows [panel 2P | panel 2P+1] (a random gather of
+//      256-byte rows runs at full HBM bandwidth, one of 128-byte rows does not).  Packed: N^2/16
+//      bytes.  A pair and the dominator counts of its columns are owned by one rank (P mod world).
+//   7. Peeling: front k = columns whose count is 0.  Every front row is read exactly once per pair,
+//      rows are summed bit-sliced (carry-save adders), subtracted from bit-sliced counts, and
+//      "count == 0" is the NOR of the planes.  One persistent cooperative kernel peels all fronts:
+//      k_peel_dynamic re-balances the work over the CTAs for every front (one GPU); on several GPUs
+//      k_peel_persistent<true> (fixed ownership) also exchanges front membership over NVLink peer
+//      memory inside the kernel.
 #include <cooperative_groups.h>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
@@ -839,7 +841,7 @@ namespace cg = cooperative_groups;
 
 constexpr int PEEL_WARPS = 8;
 constexpr int PEEL_LOG_WARPS = 3;
-constexpr int PEEL_STAGES = 4;                      // gather-ring stages (32 row slots each) per warp
+constexpr int PEEL_STAGES = 4;                      // bulk-copy gather-ring stages per warp (fixed-ownership kernel)
 constexpr int PEEL_UP = 9;                          // register planes 8 .. 2^11 (+ ones, twos, fours)
 constexpr int PEEL_RP = 3 + PEEL_UP;                // 12 planes per warp: up to 4095 rows per pass
 constexpr int PEEL_PM = PEEL_RP + PEEL_LOG_WARPS;   // merged over 8 warps: 15 planes (8*4095 < 2^15)
@@ -854,7 +856,7 @@ constexpr int PEEL_ROWS_PER_WARP = (1 << PEEL_RP) - 32;
 constexpr int PEEL_ROWS_PER_PASS = PEEL_WARPS * PEEL_ROWS_PER_WARP;
 
 
-constexpr int PEEL_STAGE_ROWS = 8;                  // 256-byte super-rows per gather-ring stage (4 KB)
+constexpr int PEEL_STAGE_ROWS = 8;                  // 256-byte super-rows per gather-ring stage (2 KB)
 
 struct PeelShared {
     alignas(128) uint32_t merge[PEEL_WARPS][PEEL_PM][PW2];                          // both panels of the pair
@@ -1126,11 +1128,11 @@ __device__ __forceinline__ void csa8(uint32_t& ones, uint32_t& twos, uint32_t& f
 }
 
 // ---- bulk-copy gather ring -------------------------------------------------------------------------
-// A front row's 128-byte segment is fetched with cp.async.bulk (the TMA engine's 1-D copy): every
-// lane issues the copy of a DIFFERENT row, so one warp instruction starts up to 32 row fetches
-// (a per-lane load moves one row per warp instruction and made the gather LSU-issue bound).  Copies
-// complete on an mbarrier; each warp owns PEEL_STAGES stages of 32 row slots in shared memory and
-// consumes one stage while the next is in flight.
+// Fixed-ownership kernel: a front row's 256-byte super-row is fetched with cp.async.bulk (the TMA
+// engine's 1-D copy), every lane issuing the copy of a DIFFERENT row.  Copies complete on an
+// mbarrier; each warp owns PEEL_STAGES stages of PEEL_STAGE_ROWS row slots in shared memory and
+// consumes the oldest stage while the others are in flight.  (The instruction is warp-uniform, so
+// the lanes are issued one after another; k_peel_dynamic uses cp.async.cg instead, see below.)
 struct Ring {
     uint32_t* slots;             // [PEEL_STAGES][PEEL_STAGE_ROWS][PW2]
     uint64_t* bars;              // [PEEL_STAGES] mbarriers
