@@ -26,6 +26,12 @@
 //      k_peel_dynamic re-balances the work over the CTAs for every front (one GPU); on several GPUs
 //      k_peel_persistent<true> (fixed ownership) also exchanges front membership over NVLink peer
 //      memory inside the kernel.
+//
+// File map: geometry and workspace layout - sort / unique / labels - tile kernels (word_fail, f2_mask,
+// slab_out, counts_flush, tile_offdiag, tile_diag) - one-front-per-launch peel (k_front_detect /
+// k_mask_to_list / k_front_apply) - fixed-ownership persistent peel with the multi-rank exchange
+// (world_barrier, k_peel_persistent) - load-balanced persistent peel (world_barrier_seg,
+// k_peel_dynamic) - host side (launch_tiles, build, detect / apply, peel_persistent) - C entry points.
 #include <cooperative_groups.h>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
