@@ -326,3 +326,55 @@ def lsmop(which, X, m, sublen=None, off=None, nk=5):
                        axis=1, keepdims=True, dtype=F32)
         f[:, m - 1:m] = (1 + gs) * h
         return f
+
+
+# --------------------------------------------------------------------------- #
+# SPEA2 fitness and truncation   algorithms/mo/spea2.py
+# --------------------------------------------------------------------------- #
+def pairwise_euclidean_dist(x, y):
+    """d[i, j] = || x[i] - y[j] ||_2 in float32.  src/evox/utils/common.py:33-56
+    (`pairwise_func` over `euclidean_dist` = `jnp.linalg.norm(x - y)`)."""
+    x = np.asarray(x, F32)
+    y = np.asarray(y, F32)
+    diff = (x[:, None, :] - y[None, :, :]).astype(F32)
+    return np.sqrt((diff * diff).astype(F32).sum(-1, dtype=F32)).astype(F32)
+
+
+def spea2_cal_fitness(obj):
+    """SPEA2 fitness = density + raw fitness.  src/evox/algorithms/mo/spea2.py:21-37.
+
+    strength s[i] = rows i dominates (:25); raw r[j] = sum of s over j's dominators (:27-29);
+    density d = 1 / (distance to the k-th nearest other row + 2) with k = floor(sqrt(6)) = 2, i.e.
+    sorted-distance index 1 once the diagonal is +inf (:31-36)."""
+    obj = np.asarray(obj, F32)
+    n = obj.shape[0]
+    dom = dominate_relation(obj, obj)
+    s = dom.sum(1).astype(np.int32)
+    r = (dom * s[:, None]).sum(0).astype(np.int32)
+    dis = pairwise_euclidean_dist(obj, obj)
+    dis[np.arange(n), np.arange(n)] = np.inf
+    dis = np.sort(dis, axis=1)
+    kth = int(np.floor(np.sqrt(6))) - 1
+    d = (F32(1) / (dis[:, kth] + F32(2))).astype(F32)
+    return (d + r.astype(F32)).astype(F32)
+
+
+def spea2_truncation(obj, k, mask):
+    """Archive truncation: k times remove the valid row whose nearest valid neighbour is closest
+    (ties: lowest index, `jnp.argsort` is stable); returns the rows kept.
+    src/evox/algorithms/mo/spea2.py:40-67.  As in the reference, k must not exceed the number of valid
+    rows minus one (its while_loop would not terminate otherwise)."""
+    obj = np.asarray(obj, F32)
+    mask = np.asarray(mask, bool)
+    n = obj.shape[0]
+    dis = pairwise_euclidean_dist(obj, obj)
+    dis[np.arange(n), np.arange(n)] = np.inf
+    dis = np.where(mask[:, None] & mask[None, :], dis, F32(np.inf)).astype(F32)
+    keep = np.ones(n, bool)
+    assert k <= max(0, int(mask.sum()) - 1), "spea2_truncation: k exceeds what the reference's loop can remove"
+    for _ in range(int(k)):
+        idx = int(np.argsort(dis.min(axis=1), kind="stable")[0])
+        keep[idx] = False
+        dis[idx, :] = np.inf
+        dis[:, idx] = np.inf
+    return keep & mask

@@ -237,6 +237,7 @@ jnp.ones = _ones
 jnp.empty = _zeros           # XLA materialises jnp.empty as zeros
 jnp.lexsort = _lexsort
 jnp.argsort = _argsort
+jnp.sort = _wrapfn(lambda x, axis=-1: np.sort(x, axis=axis, kind="stable"))
 jnp.unique = _unique
 jnp.c_ = _CClass()
 jnp.r_ = _RClass()
@@ -395,3 +396,24 @@ def install():
     maf = types.SimpleNamespace(MaF1=ns["MaF1"])
     return types.SimpleNamespace(utils=utils, nd=nd, dtlz=dtlz, lsmop=lsmop, maf=maf,
                                  asarray=_asarray)
+
+
+def lift(rel, names, ns):
+    """Execute only the named top-level functions / classes of a reference source file in `ns`
+    (for files whose module top imports more of jax / evox than the shim provides)."""
+    tree = ast.parse((REF_SRC / rel).read_text())
+    for node in tree.body:
+        if isinstance(node, (ast.FunctionDef, ast.ClassDef)) and node.name in names:
+            exec(compile(ast.Module([node], []), rel, "exec"), ns)
+    return ns
+
+
+def lift_spea2():
+    """cal_fitness and _truncation of algorithms/mo/spea2.py:21-67 with the utils they call."""
+    from functools import partial
+    ns = {"jax": jax, "jnp": jnp, "jit": _jit, "vmap": _vmap, "partial": partial}
+    lift("utils/common.py", ("pairwise_func", "euclidean_dist", "pairwise_euclidean_dist", "_dominate",
+                             "dominate_relation"), ns)
+    lift("algorithms/mo/spea2.py", ("cal_fitness", "_truncation"), ns)
+    return types.SimpleNamespace(cal_fitness=ns["cal_fitness"], truncation=ns["_truncation"])
+
