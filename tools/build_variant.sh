@@ -1,5 +1,7 @@
 #!/bin/bash
-# usage: tools/build_variant.sh <name> [-DEVX_...=...]   -> tools/variants/libevoxmo_<name>.so  (experiments only)
+# usage: tools/build_variant.sh <name> [-DEVX_WPG=.. -DEVX_CW=.. -DEVX_CC=..]  -> tools/variants/libevoxmo_<name>.so
+# Builds nds.cu with other constants into a separate library so that several variants can be timed on ONE GPU box in one
+# call (copy a variant over evox_b200/libevoxmo.so on the box, run tools/peel_times.py): profiles/r1_variants_constants.log.
 set -e
 name=$1; shift
 cd "$(dirname "$0")/.."
