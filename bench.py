@@ -43,6 +43,8 @@ def parse():
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
                     help="multi-GPU front exchange: in-kernel peer stores (default) or one NCCL all-gather per front")
     ap.add_argument("--no-nsga2", action="store_true", help="skip the NSGA-II generations/s side measurement")
+    ap.add_argument("--verify-rows", type=int, default=2048,
+                    help="rows of the sampled exactness check run on the ranks of the last timed step (outside the timing)")
     return ap.parse_args()
 
 
@@ -145,6 +147,28 @@ def run_reference(args):
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
+def verify_last_step(torch, dist, x, ranks, world, rank, rows):
+    """Outside the timed region: the ranks the LAST timed step produced are held to the peel's defining
+    identity (evox_b200/_verify.py) on `rows` sampled rows against all n, and to "every front index is
+    used".  With several GPUs every rank checks its own share of the sample on its own copy of the result
+    and the verdicts are all-reduced, so a rank that ended with different ranks fails the run."""
+    from evox_b200._verify import fronts_contiguous, rank_mismatches_sampled
+    n = x.shape[0]
+    g = torch.Generator(device="cuda").manual_seed(12345)
+    idx = torch.randperm(n, device="cuda", generator=g)[:min(rows, n)]
+    bad = rank_mismatches_sampled(x, ranks, idx[rank::world]) + (0 if fronts_contiguous(ranks) else 1)
+    t = torch.tensor([bad, int(ranks.long().sum() % 1000003)], device="cuda", dtype=torch.int64)
+    same = True
+    if world > 1:
+        lo, hi = t[1:].clone(), t[1:].clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        same = bool((lo == hi).all())                    # every rank holds the same rank vector
+        dist.all_reduce(t[:1], op=dist.ReduceOp.SUM)
+    return {"rows": int(idx.numel()), "mismatches": int(t[0]), "ranks_identical_on_all_gpus": same,
+            "ok": int(t[0]) == 0 and same, "how": "rank[j] == 1 + max rank of j's dominators, sampled j vs all rows, plain torch"}
+
+
 def run_ours(args):
     import numpy as np
     import torch
@@ -233,6 +257,7 @@ def run_ours(args):
         step_e2e()
         ms_e2e = timed(step_e2e, K)
         assert bool((rank_host.cuda() == rank_out).all()), "host and device entry points disagree"
+        verified = verify_last_step(torch, dist, x, rank_out, world, rank, args.verify_rows)
     else:
         from evox_b200.distributed import FusedShardedNonDominatedSort, ShardedNonDominatedSort
         sh = (ShardedNonDominatedSort if args.exchange == "nccl" else FusedShardedNonDominatedSort)(n, m)
@@ -257,7 +282,15 @@ def run_ours(args):
             torch.cuda.current_stream().synchronize()
         step_e2e()
         ms_e2e = timed(step_e2e, K)
+        verified = verify_last_step(torch, dist, x, holder["r"], world, rank, args.verify_rows)
 
+    if not verified["ok"]:
+        if rank == 0:
+            print(json.dumps({"metric": METRIC, "error": "ranks of the last timed step failed the sampled exactness check",
+                              "verified": verified, "n_gpus": world}), flush=True)
+        if world > 1:
+            dist.destroy_process_group()
+        sys.exit(3)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -269,7 +302,7 @@ def run_ours(args):
             "data": "synthetic",
             "config": {"workload": workload_name(n, m), "fronts": fronts, "parallelism": f"column-panel shards x{world}" + (f", front exchange: {args.exchange}" if world > 1 else ""),
                        "l2": "working set (packed bit matrix %.1f GB) >> 126 MB L2; no flush needed" % (n * n / 16 / 1e9)},
-            "clocks": clocks, "gpu_launches": launches,
+            "clocks": clocks, "gpu_launches": launches, "verified": verified,
             "e2e": {"value": pairs * K / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": n * m * 4,
                     "d2h_bytes_per_step": n * 4, "ms_per_step": ms_e2e / K}}
     if stages:

@@ -19,7 +19,8 @@ void set_error(const char* fmt, ...) {
 }
 
 // Grow-only arena, one per device, for the entry points that take host buffers.
-static std::mutex g_arena_mu;
+static std::recursive_mutex g_arena_mu;
+std::recursive_mutex& arena_mutex() { return g_arena_mu; }
 static void* g_arena_ptr[64] = {nullptr};
 static size_t g_arena_bytes[64] = {0};
 
@@ -27,7 +28,7 @@ int arena_get(size_t bytes, void** ptr) {
     int dev = 0;
     EVX_CUDA(cudaGetDevice(&dev));
     EVX_REQUIRE(dev >= 0 && dev < 64, EVX_ERR_ARG, "arena: device index %d out of range", dev);
-    std::lock_guard<std::mutex> lock(g_arena_mu);
+    std::lock_guard<std::recursive_mutex> lock(g_arena_mu);
     if (g_arena_bytes[dev] < bytes) {
         if (g_arena_ptr[dev]) {
             EVX_CUDA(cudaDeviceSynchronize());
@@ -100,6 +101,7 @@ extern "C" int evx_probe_compare_rate(int32_t m, int64_t iters, double* pairs_pe
     int dev = 0, sms = 0;
     EVX_CUDA(cudaGetDevice(&dev));
     EVX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    std::lock_guard<std::recursive_mutex> hold(arena_mutex());
     uint32_t* sink = nullptr;
     int rc = arena_get(256, reinterpret_cast<void**>(&sink));
     if (rc) return rc;

@@ -5,6 +5,8 @@
 #include <stdio.h>
 #include <stdarg.h>
 
+#include <mutex>
+
 #include "../../include/evoxmo.h"
 
 namespace evx {
@@ -66,7 +68,10 @@ __device__ __forceinline__ uint32_t float_key_nan_last(float v) {
 int small_nds_launch(const float* x, int n, int m, int* rank, uint32_t* bits, int words, int* count, int* fronts_out,
                      cudaStream_t s);
 
-// Grow-only device arena for the *_host_* entry points (one per device, mutex-guarded).
+// Grow-only device arena for the *_host_* entry points (one per device).  A host entry point holds
+// arena_mutex() from arena_get until its last copy has finished: two host threads calling *_host_*
+// functions are serialised instead of sharing (or freeing) each other's scratch.
 int arena_get(size_t bytes, void** ptr);
+std::recursive_mutex& arena_mutex();
 
 }  // namespace evx

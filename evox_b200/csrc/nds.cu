@@ -2637,6 +2637,7 @@ extern "C" int evx_nds_host_f32(const float* x_host, int64_t n, int32_t m, int32
     const size_t wsb = evx_nds_workspace_bytes(n, m);
     EVX_REQUIRE(wsb != 0, EVX_ERR_ARG, "evx_nds_host_f32: n too large");
     const size_t xb = align_up(sizeof(float) * (size_t)n * m, 256), rb = align_up(sizeof(int) * (size_t)n, 256);
+    std::lock_guard<std::recursive_mutex> hold(arena_mutex());      // the arena is this call's until the D2H copy is done
     void* base = nullptr;
     int rc = arena_get(xb + rb + wsb, &base);
     if (rc) return rc;

@@ -378,3 +378,65 @@ def spea2_truncation(obj, k, mask):
         dis[idx, :] = np.inf
         dis[:, idx] = np.inf
     return keep & mask
+
+
+# --------------------------------------------------------------------------- #
+# NSGA-II variation      operators/crossover/sbx.py:8-40,
+#                                      operators/mutation/pm_mutation.py:7-54, algorithms/mo/nsga2.py:85
+# --------------------------------------------------------------------------- #
+def simulated_binary(x, mu, sign, keep, pair, pro_c, dis_c):
+    """sbx.py:8-40, type 1, with the four random arrays passed in instead of drawn:
+    mu = uniform(mu_key) [pairs, d]; sign = randint(beta1_key, 0, 2); keep = uniform(beta2_key);
+    pair = uniform(beta3_key) [pairs, 1]."""
+    x = np.asarray(x, F32)
+    n = x.shape[0]
+    p1, p2 = x[: n // 2], x[n // 2: n // 2 * 2]
+    with np.errstate(invalid="ignore", divide="ignore"):
+        beta = np.where(mu <= 0.5, np.power(F32(2) * mu, F32(1 / (dis_c + 1))), F32(0)).astype(F32)      # :16
+        beta = np.where(mu > 0.5, np.power(F32(2) - F32(2) * mu, F32(-1 / (dis_c + 1))), beta).astype(F32)   # :17
+    beta = (beta * np.where(sign & 1, F32(-1), F32(1))).astype(F32)                                      # :18-20
+    beta = np.where(keep < 0.5, F32(1), beta)                                                            # :21
+    beta = np.where(np.tile(pair > F32(pro_c), (1, x.shape[1])), F32(1), beta).astype(F32)              # :22-24
+    mid, dev = (p1 + p2) / F32(2), beta * (p1 - p2) / F32(2)
+    out = np.vstack((mid + dev, mid - dev)).astype(F32)                                                  # :26-34
+    if n % 2:
+        out = np.r_[out, x[-1:]]                                                                         # :35-36
+    return out
+
+
+def polynomial(x, lb, ub, site_u, mu, pro_m, dis_m):
+    """pm_mutation.py:7-54 with site_u = uniform(subkey1), mu = uniform(subkey2), both [2*(n//2), d]."""
+    x = np.asarray(x, F32)
+    pop = x if x.shape[0] == 1 else x[: (x.shape[0] // 2) * 2]
+    n, d = pop.shape
+    site = site_u < F32(pro_m / d)                                                                       # :16
+    lower, upper = np.tile(np.asarray(lb, F32), (n, 1)), np.tile(np.asarray(ub, F32), (n, 1))
+    pop = np.maximum(np.minimum(pop, upper), lower)                                                      # :21
+    e1, e = F32(dis_m + 1.0), F32(1.0 / (dis_m + 1))
+    one, two, half = F32(1), F32(2), F32(0.5)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        temp = site & (mu <= 0.5)                                                                        # :19
+        norm = np.where(temp, (pop - lower) / (upper - lower), F32(0)).astype(F32)
+        pop = np.where(temp, pop + (upper - lower) * (np.power(two * mu + (one - two * mu) * np.power(one - norm, e1), e) - one),
+                       pop).astype(F32)                                                                  # :23-35
+        temp = site & (mu > 0.5)                                                                         # :37
+        norm = np.where(temp, (upper - pop) / (upper - lower), F32(0)).astype(F32)
+        pop = np.where(temp, pop + (upper - lower) * (one - np.power(two * (one - mu) + two * (mu - half) * np.power(one - norm, e1), e)),
+                       pop).astype(F32)                                                                  # :38-51
+    if x.shape[0] % 2:
+        pop = np.r_[pop, x[-1:]]                                                                         # :52-53
+    return pop
+
+
+def nsga2_variation(pop, lb, ub, pro_c, dis_c, pro_m, dis_m, seed, generation):
+    """nsga2.py:78-85 (`ask`: crossover -> mutation -> clip) on the uniforms csrc/variation.cu draws
+    (oracle/philox.py) instead of jax.random's."""
+    from . import philox
+    pop = np.asarray(pop, F32)
+    n, d = pop.shape
+    if n < 2:
+        return np.clip(pop, lb, ub).astype(F32)
+    dr = philox.variation_draws(n, d, seed, generation)
+    c = simulated_binary(pop, dr["sbx_mu"], dr["sbx_sign"], dr["sbx_keep"], dr["sbx_pair"], pro_c, dis_c)
+    c = polynomial(c, lb, ub, dr["pm_site"], dr["pm_mu"], pro_m, dis_m)
+    return np.clip(c, np.asarray(lb, F32), np.asarray(ub, F32)).astype(F32)

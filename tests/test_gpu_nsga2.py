@@ -64,6 +64,40 @@ def test_polynomial_mutation_rate_and_bounds():
     assert torch.equal(a, b) and not torch.equal(a, c)          # reproducible per (seed, generation)
 
 
+@pytest.mark.parametrize("i", range(5))
+def test_variation_values_match_reference_source(i):
+    """Value parity for a given draw: the kernel's uniforms are regenerated on the CPU (oracle/philox.py),
+    pushed through the reference's own `simulated_binary` / `polynomial` source on the jax shim
+    (tests/golden/make_golden_variation.py, fixtures committed) and the kernel must reproduce the
+    result.  Tolerance: 1e-6 relative plus 2e-6 of the gene's range - CUDA powf and NumPy's float32 pow
+    differ by a few ulp, and pm_mutation.py:27-33 subtracts 1 from a power close to 1."""
+    from pathlib import Path
+    G = np.load(Path(__file__).parent / "golden" / "variation_outputs.npz")
+    pc, dc, pm, dm = (float(v) for v in G[f"var{i}_par"])
+    seed, gen = (int(v) for v in G[f"var{i}_seed"])
+    pop, lb, ub = (torch.from_numpy(G[f"var{i}_{k}"]).cuda() for k in ("pop", "lb", "ub"))
+    out = _vary(pop, lb, ub, pc, dc, pm, dm, seed, gen).cpu().numpy()
+    want = G[f"var{i}_out"]
+    span = (G[f"var{i}_ub"] - G[f"var{i}_lb"])[None, :]
+    err = np.abs(out - want)
+    assert (err <= 1e-6 * np.abs(want) + 2e-6 * span).all(), (i, float(err.max()))
+    assert (out != G[f"var{i}_pop"]).any()                     # the case does exercise the operators
+
+
+def test_variation_values_large_vs_oracle():
+    """Same comparison at the configs[2] shape (pop 100k, d = 12) against the NumPy restatement
+    (oracle_np.nsga2_variation, itself pinned to the reference source by tests/test_oracle_variation.py)."""
+    from oracle import oracle_np as O
+    n, d = 100_000, 12
+    rng = np.random.default_rng(17)
+    pop = rng.random((n, d), dtype=np.float32)
+    lb, ub = np.zeros(d, np.float32), np.ones(d, np.float32)
+    out = _vary(torch.from_numpy(pop).cuda(), torch.from_numpy(lb).cuda(), torch.from_numpy(ub).cuda(), seed=11, gen=250)
+    want = O.nsga2_variation(pop, lb, ub, 1.0, 20.0, 1.0, 20.0, 11, 250)
+    err = np.abs(out.cpu().numpy() - want)
+    assert (err <= 1e-6 * np.abs(want) + 2e-6).all(), float(err.max())
+
+
 def test_nsga2_converges_on_dtlz2():
     """configs[0]-style run (pop 100, M=3): after 100 generations the population sits on the unit
     sphere of DTLZ2 (sum f^2 = 1 on the true front) - an end-to-end sanity check of variation +

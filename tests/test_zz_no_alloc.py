@@ -4,7 +4,8 @@ Some callers of this library only ever hold their input and output buffers - a c
 inside another framework, a callback that runs while that framework's allocator is locked - and so
 cannot pass the workspace evx_nds_f32 asks for.  This entry point keeps its scratch in a fixed array
 inside the library instead.  The test calls it through the C ABI and checks its ranks against
-evx_nds_f32 (exact, as for every rank comparison in this suite), twice in a row on the same device:
+evx_nds_f32 and against the CPU oracle (exact, as for every rank comparison in this suite), twice in
+a row on the same device:
 the second call runs on a smaller, different population, so anything left over from the first call in
 the shared scratch would show up as a wrong rank.  The file name sorts last on purpose.
 """
@@ -36,6 +37,7 @@ def _noalloc_ranks(L, x):
 
 def test_noalloc_matches_workspace_entry_point_twice():
     from evox_b200._lib import lib
+    from oracle import oracle_c as C
     L = lib()
     rng = np.random.default_rng(2024)
     first = rng.random((4096, 3), dtype=np.float32)           # the documented maximum
@@ -47,6 +49,8 @@ def test_noalloc_matches_workspace_entry_point_twice():
         got = _noalloc_ranks(L, x)
         want = _reference_ranks(L, x)
         assert torch.equal(got, want), (host.shape, (got != want).nonzero()[:5])
+        # ... and both agree with the dense-matrix oracle, so the two kernels cannot be wrong together
+        assert (got.cpu().numpy() == C.non_dominated_sort(host)).all(), host.shape
 
 
 def test_noalloc_rejects_oversize_and_allocates_nothing():
