@@ -25,6 +25,8 @@ _SIGNATURES = {
     "evx_crowding_workspace_bytes": (c_sz, [c_i64, c_i32]),
     "evx_crowding_distance_f32": (ctypes.c_int, [c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_sz, c_vp]),
     "evx_crowding_distance_sort_f32": (ctypes.c_int, [c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_sz, c_vp]),
+    "evx_non_dominate_workspace_bytes": (c_sz, [c_i64, c_i32]),
+    "evx_non_dominate_f32": (ctypes.c_int, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_i64, c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
     "evx_eval_dtlz_f32": (ctypes.c_int, [c_i32, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp]),
     "evx_eval_maf1_f32": (ctypes.c_int, [c_vp, c_i64, c_i32, c_i32, c_vp, c_vp]),
     "evx_lsmop_groups": (ctypes.c_int, [c_i32, c_i32, c_vp, c_vp]),

@@ -4,7 +4,7 @@
     rank[j] == 1 + max(rank[i] for i dominating j)      (0 when nothing dominates j),
 which follows from the peel of non_dominate.py:74-113: a row leaves in the front after its last
 dominator left.  Checking the identity for a sample of rows j against ALL rows i costs
-len(sample) * n compares, so it runs at N = 1M where no dense oracle can.  Used by the `-m gpu`
+len(sample) * n compares, so it runs at N = 1M where no dense N x N check can.  Used by the `-m gpu`
 tests and by bench.py's `verified` field (each rank of a multi-GPU run checks its share of the sample).
 """
 import torch

@@ -104,8 +104,10 @@ static CdLayout cd_layout(int64_t n, int m) {
     return L;
 }
 
+// `nv_known`: device int holding the number of valid rows when the caller already has it (the fused
+// survivor selection reads it off the rank histogram); nullptr = count the mask here.
 static int crowding(const float* costs, const uint8_t* mask, int64_t n, int m, float* dist, char* ws,
-                    const CdLayout& L, cudaStream_t s) {
+                    const CdLayout& L, cudaStream_t s, const int* nv_known = nullptr) {
     const int T = 256;
     const int64_t nm = n * m;
     CdScal* sc = reinterpret_cast<CdScal*>(ws + L.sc);
@@ -114,9 +116,13 @@ static int crowding(const float* costs, const uint8_t* mask, int64_t n, int m, f
     int* vA = reinterpret_cast<int*>(ws + L.valsA);
     int* vB = reinterpret_cast<int*>(ws + L.valsB);
     float* dk = reinterpret_cast<float*>(ws + L.dk);
-    EVX_CUDA(cudaMemsetAsync(sc, 0, sizeof(CdScal), s));
-    k_cd_count<<<(unsigned)ceil_div(ceil_div(n, 32) * 32, T), T, 0, s>>>(mask, n, sc);
-    EVX_LAUNCH_CHECK();
+    if (nv_known) {
+        sc = reinterpret_cast<CdScal*>(const_cast<int*>(nv_known));
+    } else {
+        EVX_CUDA(cudaMemsetAsync(sc, 0, sizeof(CdScal), s));
+        k_cd_count<<<(unsigned)ceil_div(ceil_div(n, 32) * 32, T), T, 0, s>>>(mask, n, sc);
+        EVX_LAUNCH_CHECK();
+    }
     k_cd_keys<<<(unsigned)ceil_div(nm, T), T, 0, s>>>(costs, mask, n, m, L.obj_bits, kA, vA);
     EVX_LAUNCH_CHECK();
     size_t tb = L.tmp_bytes;
@@ -126,6 +132,29 @@ static int crowding(const float* costs, const uint8_t* mask, int64_t n, int m, f
     k_cd_sum<<<(unsigned)ceil_div(n, T), T, 0, s>>>(dk, mask, n, m, dist);
     EVX_LAUNCH_CHECK();
     return EVX_OK;
+}
+
+static int crowding_sort(const float* costs, const uint8_t* mask, int64_t n, int m, int32_t* order, char* base,
+                         cudaStream_t s, const int* nv_known) {
+    const CdLayout L = cd_layout(n, m);
+    float* dist = reinterpret_cast<float*>(base + L.dist);
+    int rc = crowding(costs, mask, n, m, dist, base, L, s, nv_known);
+    if (rc) return rc;
+    uint32_t* kA = reinterpret_cast<uint32_t*>(base + L.keysA);
+    uint32_t* kB = reinterpret_cast<uint32_t*>(base + L.keysB);
+    int* vA = reinterpret_cast<int*>(base + L.valsA);
+    k_cd_sortkeys<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(dist, n, kA, vA);
+    EVX_LAUNCH_CHECK();
+    size_t tb = L.tmp_bytes;
+    EVX_CUDA(cub::DeviceRadixSort::SortPairs(base + L.tmp, tb, kA, kB, vA, order, (int)n, 0, 32, s));
+    return EVX_OK;
+}
+
+// For select.cu: crowding_distance_sort with the valid-row count already on the device.
+int crowding_sort_known(const float* costs, const uint8_t* mask, const int* nv_dev, int64_t n, int m, int32_t* order,
+                        void* ws, cudaStream_t s) {
+    return crowding_sort(costs, mask, n, m, order, reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(ws), 256)), s,
+                         nv_dev);
 }
 
 }  // namespace evx
@@ -160,18 +189,6 @@ extern "C" int evx_crowding_distance_sort_f32(const float* costs, const uint8_t*
                                               int32_t* order, void* ws, size_t ws_bytes, void* stream) {
     int rc = cd_check("evx_crowding_distance_sort_f32", costs, n, m, order, ws, ws_bytes);
     if (rc || n == 0) return rc;
-    cudaStream_t s = (cudaStream_t)stream;
     char* base = reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(ws), 256));
-    const CdLayout L = cd_layout(n, m);
-    float* dist = reinterpret_cast<float*>(base + L.dist);
-    rc = crowding(costs, mask, n, m, dist, base, L, s);
-    if (rc) return rc;
-    uint32_t* kA = reinterpret_cast<uint32_t*>(base + L.keysA);
-    uint32_t* kB = reinterpret_cast<uint32_t*>(base + L.keysB);
-    int* vA = reinterpret_cast<int*>(base + L.valsA);
-    k_cd_sortkeys<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(dist, n, kA, vA);
-    EVX_LAUNCH_CHECK();
-    size_t tb = L.tmp_bytes;
-    EVX_CUDA(cub::DeviceRadixSort::SortPairs(base + L.tmp, tb, kA, kB, vA, order, (int)n, 0, 32, s));
-    return EVX_OK;
+    return crowding_sort(costs, mask, n, m, order, base, (cudaStream_t)stream, nullptr);
 }

@@ -57,32 +57,25 @@ constexpr int TILE_ROWS_PER_WARP = 128;                 // slabs per warp = 128 
 constexpr int APPLY_WARPS = 8;
 constexpr int SMALL_PATH_MAX_N = 1024;   // populations of at most one panel take the direct small path
 constexpr int PEEL_MAX_GRID = 1024;  // upper bound on the CTAs of the persistent peel kernel
-constexpr int PEEL_PM_MAX = 16;      // >= merged count planes of the persistent peel (PEEL_PM)
 constexpr int PEEL_KMAX = 24;      // count planes the load-balanced peel kernel supports (N < 16M)
 constexpr int ANY_SLOTS = 64;
 
 struct Scal {
     int U;          // unique non-NaN rows
     int n_nan;      // rows holding a NaN
-    int nf[2];      // size of the current front list, double buffered by front parity
+    int nf[2];      // one-front-per-launch peel: size of the current front list, double buffered by front parity
     int any[ANY_SLOTS];
-    int nf3[3];     // persistent peel: front sizes, triple buffered (read k, append k+1, clear k+2)
-    int fronts;     // persistent peel: number of fronts found
-    unsigned int barrier;   // persistent peel: grid barrier arrivals (monotonic)
-    unsigned int go;        // fused multi-rank peel: release word written by CTA 0
-    int abort;              // fused multi-rank peel: a peer barrier timed out
-    int pub3[3];            // fused multi-rank peel: members this rank published, triple buffered
-    int xcnt[8];            // fused multi-rank peel: per-rank member counts of the current front
-    int xtotal;             // fused multi-rank peel: their sum (-1: time-out)
+    int fronts;     // persistent peel: number of fronts found (-1: a peer timed out)
+    unsigned int barrier;   // persistent peel: grid barrier arrivals (monotonic within a launch)
     unsigned long long dbg[8];   // persistent peel: ns spent by CTA 0 / last CTA in accumulate, merge+commit, barrier
-    unsigned long long bdbg[8];  // world barrier, CTA 0: ns in {own fence+arrive, local wait, fence, send, peer wait, fence, release}
+    unsigned long long bdbg[8];  // world barrier, CTA 0: ns in {fence + arrive, waiting for the messages, acquire fence}
 };
 
 struct Layout {
     int64_t n, npad;
     int m, world, rank, np, npl, npl_max;
     size_t keys, idxA, idxB, skeyA, skeyB, flags, incl, cubtmp, cubtmp_bytes, ucols, row2u, count,
-        rank_u, flist, flist2, cplanes, mask, scal, bits, total, tcols, bkeyA, bkeyB, label, items, partials, pdone, pcnt;
+        rank_u, flist, flist2, cplanes, mask, scal, bits, total, tcols, bkeyA, bkeyB, label, partials, pdone, pcnt;
     int kplanes;
     int64_t bits_words;
 };
@@ -153,7 +146,6 @@ static Layout make_layout(int64_t n, int m, int world, int rank) {
     while ((1ll << L.kplanes) <= L.npad) ++L.kplanes;          // counts < npad fit in kplanes bits
     L.cplanes = take(sizeof(uint32_t) * (size_t)L.npl_max * (L.kplanes + 1) * PW);
     L.mask = take(sizeof(uint32_t) * (size_t)L.npl_max * PW * world);
-    L.items = take(sizeof(int) * 4 * (size_t)(L.npl_max + 2 * PEEL_MAX_GRID));
     L.partials = take(sizeof(uint32_t) * (size_t)(PEEL_MAX_GRID + L.npl_max / 2 + 1) * PEEL_KMAX * 64);
     L.pcnt = take(sizeof(int) * 3 * (size_t)(L.npl_max + 2));          // per-panel front sizes, triple buffered
     L.pdone = take(sizeof(unsigned int) * 2 * (size_t)L.npl_max);      // arrivals, commits
@@ -832,46 +824,21 @@ k_front_apply(const uint32_t* __restrict__ bits, int* __restrict__ count, const 
 
 
 // ------------------------------------------------------------------------------------------------
-// stage 3b: the whole peel as ONE persistent cooperative kernel (single-rank path)
+// stage 3b: the whole peel as ONE persistent cooperative kernel
 // ------------------------------------------------------------------------------------------------
-// Each CTA owns a fixed set of panels (heaviest first, dealt boustrophedon so the triangular panel
-// sizes balance).  The dominator counts of a panel live BIT-SLICED (in shared memory when they fit,
-// else in global memory), owned by that CTA alone: plane p, word w holds bit p of the counts of
-// columns 32w..32w+31.  Per front and panel: the CTA's 16 warps stream the front's 128-byte row
-// segments (lane <-> word, 32 rows in flight per warp) into carry-save adders, the per-warp sums
-// are merged bit-sliced through shared memory, warp 0 subtracts the merged sum from the count
-// planes with a bit-sliced borrow chain, and "count == 0" is simply the NOR of the planes - which
-// IS the next front's membership mask for these 32 x 32 columns.  Nothing is ever expanded to
-// integers.  One grid-wide barrier per front.
-namespace cg = cooperative_groups;
-
+// The dominator counts of a panel live BIT-SLICED in global memory (L2): plane p, word w holds bit p of
+// the counts of columns 32w..32w+31.  Per front and panel pair the front's 256-byte super-rows are
+// gathered into carry-save adders (lane <-> word), the per-warp sums are merged bit-sliced through
+// shared memory, subtracted from the count planes with a bit-sliced borrow chain, and "count == 0" is
+// simply the NOR of the planes - which IS the next front's membership mask for these 32 x 32 columns.
+// Nothing is ever expanded to integers.  One barrier per front: over the grid on one GPU, over all
+// CTAs of all ranks in the fused multi-GPU peel.
 constexpr int PEEL_WARPS = 8;
 constexpr int PEEL_LOG_WARPS = 3;
-constexpr int PEEL_STAGES = 4;                      // bulk-copy gather-ring stages per warp (fixed-ownership kernel)
 constexpr int PEEL_UP = 9;                          // register planes 8 .. 2^11 (+ ones, twos, fours)
 constexpr int PEEL_RP = 3 + PEEL_UP;                // 12 planes per warp: up to 4095 rows per pass
 constexpr int PEEL_PM = PEEL_RP + PEEL_LOG_WARPS;   // merged over 8 warps: 15 planes (8*4095 < 2^15)
-static_assert(PEEL_PM <= PEEL_PM_MAX, "raise PEEL_PM_MAX");
-constexpr int PEEL_MAX_STRIPES = 16;                // CTAs that may share one heavy panel
-
-// One unit of peel work: a panel PAIR (local pair index lp), or one of `nstripes` row stripes of a heavy pair.
-struct PeelItem {
-    int lp, stripe, nstripes, slot;
-};
 constexpr int PEEL_ROWS_PER_WARP = (1 << PEEL_RP) - 32;
-constexpr int PEEL_ROWS_PER_PASS = PEEL_WARPS * PEEL_ROWS_PER_WARP;
-
-
-constexpr int PEEL_STAGE_ROWS = 8;                  // 256-byte super-rows per gather-ring stage (2 KB)
-
-struct PeelShared {
-    alignas(128) uint32_t merge[PEEL_WARPS][PEEL_PM][PW2];                          // both panels of the pair
-    alignas(128) uint32_t ring[PEEL_WARPS][PEEL_STAGES * PEEL_STAGE_ROWS][PW2];     // per-warp bulk-copy gather ring
-    alignas(8) uint64_t bars[PEEL_WARPS][PEEL_STAGES];
-    uint32_t newmask[2][32];
-    int nf;
-    int cnt[8];                 // fused multi-rank peel: members published by each rank for this front
-};
 
 struct Planes {
     uint32_t ones = 0, twos = 0, fours = 0, up[PEEL_UP] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
@@ -879,28 +846,30 @@ struct Planes {
 
 // ---- peer-visible state of the fused multi-rank peel ------------------------------------------------
 // Every rank provides one buffer in peer-mapped memory (torch symmetric memory / CUDA IPC):
-// [PeerState | list 0 | list 1], each list = world regions of `cap` ints, region r written only by
-// rank r.  A publisher reserves slots with a LOCAL atomic and writes the new front members straight
-// into its region on EVERY rank with posted stores over NVLink - no cross-GPU atomics.  The per-front
-// barrier spans all CTAs of all ranks: local arrive -> CTA 0 sends one 64-bit message (epoch, number
-// of members this rank published) to every rank -> waits for every rank's message -> local release.
+// [PeerState | per-panel front sizes x 3 | front segments A | front segments B], a full replica of the
+// front (all panels of all ranks).  The warp that commits a panel writes the panel's new members and
+// their number straight into EVERY rank's replica (posted stores over NVLink, no cross-GPU atomics).
+// The per-front barrier: every CTA fences its pushes at system scope and arrives on a LOCAL counter;
+// the last local arriver sends one 64-bit message (the epoch) to every rank; every CTA of every rank
+// polls its own rank's message words.  Messages are double buffered by epoch parity: a rank can be at
+// most one barrier ahead of a peer that has not read its previous message yet.  Epochs run on across
+// launches (PeerState::epoch_base) and every launch ends with one more barrier, after which no CTA of
+// any rank still reads the replica - so the next launch needs neither a reset of this state nor a
+// host-level hand-shake: the buffer is cleared once, by evx_nds_shard_peer_init.
 constexpr int MAX_WORLD = 8;
 struct PeerState {
-    unsigned long long xmsg[MAX_WORLD];     // (epoch << 32) | members published by rank r for the next front
+    unsigned long long xmsg[2][MAX_WORLD];  // [epoch & 1][source rank] = epoch of that rank's last arrival
     int abort;
-    unsigned int pad[47];
+    unsigned int epoch_base;                // barriers this rank has passed in all earlier launches (local use only)
+    unsigned int pad[30];
 };
 static_assert(sizeof(PeerState) == 256, "PeerState must stay 256 bytes");
 struct PeerTable {
     char* base[MAX_WORLD];
     int world, rank;
-    int64_t cap;                            // ints per region
 };
 __device__ __forceinline__ PeerState* peer_state(const PeerTable& pt, int r) {
     return reinterpret_cast<PeerState*>(pt.base[r]);
-}
-__device__ __forceinline__ int* peer_region(const PeerTable& pt, int on_rank, int which, int region) {
-    return reinterpret_cast<int*>(pt.base[on_rank] + sizeof(PeerState)) + ((size_t)which * pt.world + region) * pt.cap;
 }
 __device__ __forceinline__ unsigned long long global_ns() {
     unsigned long long t;
@@ -909,211 +878,6 @@ __device__ __forceinline__ unsigned long long global_ns() {
 }
 constexpr unsigned long long PEER_TIMEOUT_NS = 4000000000ull;      // a peer that is 4 s late is gone
 
-// Barrier over all CTAs of all ranks, which also carries the front exchange.  Publishers have written
-// this rank's new front members into the rank's OWN region only (local stores); once every local CTA
-// has arrived, CTA 0 pushes that region to every peer with coalesced stores, fences once at system
-// scope and sends one 64-bit message (epoch, member count) per peer, then waits for every peer's
-// message and releases the local CTAs.  Fills cnt_smem[r] with the number of members rank r published
-// for the coming front and returns their sum, or -1 after a time-out (every rank then leaves the
-// kernel; nothing spins forever).  `pub` is this rank's local publish counter for that front.
-__device__ __forceinline__ int world_barrier(Scal* scal, unsigned int& epoch, const PeerTable& pt, const int* pub,
-                                             int which_next, int* cnt_smem, int* nf_smem) {
-    __syncthreads();
-    ++epoch;
-    const unsigned long long t0 = global_ns();
-    unsigned long long tb = t0, tn;
-    if (threadIdx.x == 0) {
-        __threadfence();                                              // this CTA's list stores are out (local memory)
-        atomicAdd(&scal->barrier, 1u);
-    }
-    if (blockIdx.x == 0) {
-        if (threadIdx.x == 0) {
-            tn = global_ns(); scal->bdbg[0] += tn - tb; tb = tn;
-            unsigned int v;
-            do {                                                      // every local CTA has arrived
-                asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&scal->barrier) : "memory");
-            } while (v < epoch * gridDim.x);
-            __threadfence();
-            int mine;
-            asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(mine) : "l"(pub) : "memory");
-            *nf_smem = mine;
-            tn = global_ns(); scal->bdbg[1] += tn - tb; tb = tn;
-        }
-        __syncthreads();
-        const int mine = *nf_smem;
-        const int* src = peer_region(pt, pt.rank, which_next, pt.rank);
-        for (int r = 0; r < pt.world; ++r) {                          // push my region to every peer over NVLink
-            if (r == pt.rank) continue;
-            int* dst = peer_region(pt, r, which_next, pt.rank);
-            for (int i = threadIdx.x; i < mine; i += blockDim.x) dst[i] = __ldcg(src + i);
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            PeerState* me = peer_state(pt, pt.rank);
-            bool dead = false;
-            tn = global_ns(); scal->bdbg[2] += tn - tb; tb = tn;
-            __threadfence_system();                                   // the pushes are visible before the message
-            const unsigned long long msg = ((unsigned long long)epoch << 32) | (unsigned int)mine;
-            for (int r = 0; r < pt.world; ++r)                        // one message to every rank (and myself)
-                asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(&peer_state(pt, r)->xmsg[pt.rank]), "l"(msg)
-                             : "memory");
-            tn = global_ns(); scal->bdbg[3] += tn - tb; tb = tn;
-            int total = 0;
-            for (int r = 0; r < pt.world && !dead; ++r) {             // wait for every rank's message
-                unsigned long long m;
-                do {
-                    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(m) : "l"(&me->xmsg[r]) : "memory");
-                    if ((unsigned int)(m >> 32) >= epoch) break;
-                    int ab;
-                    asm volatile("ld.relaxed.sys.global.s32 %0, [%1];" : "=r"(ab) : "l"(&me->abort) : "memory");
-                    if (ab || global_ns() - t0 > PEER_TIMEOUT_NS) dead = true;
-                } while (!dead);
-                const int c = (int)(unsigned int)m;
-                scal->xcnt[r] = c;
-                total += c;
-            }
-            tn = global_ns(); scal->bdbg[4] += tn - tb; tb = tn;
-            __threadfence_system();                                   // acquire: peers' pushes are visible
-            tn = global_ns(); scal->bdbg[5] += tn - tb; tb = tn;
-            if (dead) {
-                for (int r = 0; r < pt.world; ++r)
-                    asm volatile("st.relaxed.sys.global.s32 [%0], %1;" ::"l"(&peer_state(pt, r)->abort), "r"(1) : "memory");
-                total = -1;
-            }
-            scal->xtotal = total;
-            __threadfence();
-            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&scal->go), "r"(epoch) : "memory");
-            tn = global_ns(); scal->bdbg[6] += tn - tb; tb = tn;
-        }
-    }
-    if (threadIdx.x == 0) {
-        bool dead = false;
-        if (blockIdx.x != 0) {
-            unsigned int v;
-            do {
-                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&scal->go) : "memory");
-            } while (v < epoch && global_ns() - t0 < 2 * PEER_TIMEOUT_NS);
-            if (v < epoch) dead = true;
-        }
-        int total;
-        asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(total) : "l"(&scal->xtotal) : "memory");
-        for (int r = 0; r < pt.world; ++r)
-            asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(cnt_smem[r]) : "l"(&scal->xcnt[r]) : "memory");
-        *nf_smem = dead ? -1 : total;
-    }
-    __syncthreads();
-    return *nf_smem;
-}
-
-// Warp 0, multi-rank: subtract, detect, retire, and write the new front members into this rank's
-// own region (the barrier pushes the region to the peers).
-__device__ __forceinline__ void peel_commit_world(uint32_t* cp, int K, const uint32_t* delta, int pm, int lane,
-                                                  int J, const PeerTable& pt, int which_next, int* pub,
-                                                  uint32_t* newmask_out) {
-    uint32_t borrow = 0, nz = 0;
-    for (int p = 0; p < K; ++p) {
-        const uint32_t c = cp[p * PW + lane];
-        const uint32_t d = (p < pm) ? delta[p * PW2 + lane] : 0u;
-        const uint32_t x = c ^ d;
-        const uint32_t r = x ^ borrow;
-        borrow = (~c & d) | (~x & borrow);
-        if (pm > 0) cp[p * PW + lane] = r;
-        nz |= r;
-    }
-    uint32_t alive = cp[K * PW + lane];
-    const uint32_t nw = alive & ~nz;
-    alive &= ~nw;
-    cp[K * PW + lane] = alive;
-    newmask_out[lane] = nw;
-    const int c = __popc(nw);
-    int incl = c;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-        if (lane >= o) incl += t;
-    }
-    const int total = __shfl_sync(0xFFFFFFFFu, incl, 31);
-    if (total == 0) return;                                           // warp-uniform
-    int base = 0;
-    if (lane == 0) base = atomicAdd(pub, total);                      // local slot reservation
-    base = __shfl_sync(0xFFFFFFFFu, base, 0) + incl - c;
-    const int col0 = J * TW + lane * 32;
-    int* dst = peer_region(pt, pt.rank, which_next, pt.rank) + base;  // own region, own memory; CTA 0 pushes it
-    uint32_t w = nw;
-    while (w) {
-        const int b = __ffs(w) - 1;
-        w &= w - 1;
-        *dst++ = col0 + b;
-    }
-}
-
-// Grid-wide barrier on a monotonically increasing counter (all CTAs are co-resident: cooperative
-// launch).  `epoch` counts the barriers this CTA has passed.  Only thread 0 touches global memory:
-// it also fetches the size of the front about to be processed, so 4 700 warps do not all hit the
-// same L2 word right after the barrier.
-__device__ __forceinline__ int grid_barrier(unsigned int* ctr, unsigned int& epoch, const int* nf_ptr, int* nf_smem) {
-    __syncthreads();
-    ++epoch;
-    if (threadIdx.x == 0) {
-        __threadfence();
-        atomicAdd(ctr, 1u);
-        const unsigned int target = epoch * gridDim.x;
-        unsigned int v;
-        do {
-            asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
-        } while (v < target);
-        __threadfence();
-        int nf;
-        asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(nf) : "l"(nf_ptr) : "memory");
-        *nf_smem = nf;
-    }
-    __syncthreads();
-    return *nf_smem;
-}
-
-// Warp 0: subtract `delta` (bit-sliced, `pm` planes in shared memory; null = zero) from a panel's
-// count planes, find the columns that reached zero, retire them, publish them as the next front.
-__device__ __forceinline__ void peel_commit(uint32_t* cp, int K, const uint32_t* delta, int pm, int lane,
-                                            int J, int* flist_next, int* nf_next, uint32_t* newmask_out) {
-    uint32_t borrow = 0, nz = 0;
-    for (int p = 0; p < K; ++p) {
-        const uint32_t c = cp[p * PW + lane];
-        const uint32_t d = (p < pm) ? delta[p * PW2 + lane] : 0u;         // plane p of this half of the pair
-        const uint32_t x = c ^ d;
-        const uint32_t r = x ^ borrow;
-        borrow = (~c & d) | (~x & borrow);
-        if (pm > 0) cp[p * PW + lane] = r;
-        nz |= r;
-    }
-    uint32_t alive = cp[K * PW + lane];
-    const uint32_t nw = alive & ~nz;
-    alive &= ~nw;
-    cp[K * PW + lane] = alive;
-    newmask_out[lane] = nw;
-    // publish: exclusive prefix of popcounts across the warp, one atomic per warp
-    const int c = __popc(nw);
-    int incl = c;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-        if (lane >= o) incl += t;
-    }
-    const int total = __shfl_sync(0xFFFFFFFFu, incl, 31);
-    int base = 0;
-    if (lane == 0 && total) base = atomicAdd(nf_next, total);
-    base = __shfl_sync(0xFFFFFFFFu, base, 0) + incl - c;
-    uint32_t w = nw;
-    const int col0 = J * TW + lane * 32;
-    while (w) {
-        const int b = __ffs(w) - 1;
-        w &= w - 1;
-        flist_next[base++] = col0 + b;
-    }
-}
-
-__device__ __forceinline__ void csa8(uint32_t& ones, uint32_t& twos, uint32_t& fours, uint32_t (&up)[PEEL_UP],
-                                     const uint32_t* x);
-__device__ __forceinline__ void csa8(Planes& pl, const uint32_t* x) { csa8(pl.ones, pl.twos, pl.fours, pl.up, x); }
 __device__ __forceinline__ void csa8(uint32_t& ones, uint32_t& twos, uint32_t& fours, uint32_t (&up)[PEEL_UP],
                                      const uint32_t* x) {
     uint32_t ta, tb, fa, fb, e;
@@ -1132,340 +896,9 @@ __device__ __forceinline__ void csa8(uint32_t& ones, uint32_t& twos, uint32_t& f
         e = c;
     }
 }
-
-// ---- bulk-copy gather ring -------------------------------------------------------------------------
-// Fixed-ownership kernel: a front row's 256-byte super-row is fetched with cp.async.bulk (the TMA
-// engine's 1-D copy), every lane issuing the copy of a DIFFERENT row.  Copies complete on an
-// mbarrier; each warp owns PEEL_STAGES stages of PEEL_STAGE_ROWS row slots in shared memory and
-// consumes the oldest stage while the others are in flight.  (The instruction is warp-uniform, so
-// the lanes are issued one after another; k_peel_dynamic uses cp.async.cg instead, see below.)
-struct Ring {
-    uint32_t* slots;             // [PEEL_STAGES][PEEL_STAGE_ROWS][PW2]
-    uint64_t* bars;              // [PEEL_STAGES] mbarriers
-    int issued = 0, consumed = 0;
-    uint32_t rowsp = 0;          // rows in each stage, one byte per stage
-    uint32_t phase = 0;          // bit s: parity to wait for on stage s
-};
-constexpr int PEEL_STAGE_WORDS = PEEL_STAGE_ROWS * PW2;
+__device__ __forceinline__ void csa8(Planes& pl, const uint32_t* x) { csa8(pl.ones, pl.twos, pl.fours, pl.up, x); }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\tWAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}" ::"r"(smem_u32(bar)),
-        "r"(parity)
-        : "memory");
-}
-__device__ __forceinline__ void bulk_copy_256(uint32_t* smem_dst, const uint32_t* gsrc, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 256, [%2];" ::"r"(
-                     smem_u32(smem_dst)),
-                 "l"(gsrc), "r"(smem_u32(bar))
-                 : "memory");
-}
-
-// Wait for the oldest stage and fold its super-rows into the planes of both panels of the pair.
-__device__ __forceinline__ void ring_consume(Ring& rg, int lane, Planes& pa, Planes& pb) {
-    const int st = rg.consumed & (PEEL_STAGES - 1);
-    mbar_wait(rg.bars + st, (rg.phase >> st) & 1u);
-    rg.phase ^= 1u << st;
-    const int n = (rg.rowsp >> (8 * st)) & 0xFF;
-    const uint32_t* base = rg.slots + st * PEEL_STAGE_WORDS + lane;
-    for (int r0 = 0; r0 < n; r0 += 8) {
-        uint32_t xa[8], xb[8];
-#pragma unroll
-        for (int r = 0; r < 8; ++r) {
-            const bool ok = r0 + r < n;
-            xa[r] = ok ? base[(r0 + r) * PW2] : 0u;
-            xb[r] = ok ? base[(r0 + r) * PW2 + PW] : 0u;
-        }
-        csa8(pa, xa);
-        csa8(pb, xb);
-    }
-    ++rg.consumed;
-}
-
-// Rows [0, cnt) of `list`: groups of 32 consecutive entries are dealt round-robin to the `totw` warps
-// working on this pair (all stripes together; this warp is number `wq`), starting with warp `goff`.
-// Only entries that have storage in this pair (i < rowlimit) are fetched, 16 super-rows per stage.
-// `pair` is the pair's base (row 0, word 0).
-__device__ __forceinline__ void peel_accumulate_ring(const int* list, int cnt, int goff, int wq, int totw, int lane,
-                                                     int rowlimit, const uint32_t* pair, Ring& rg, Planes& pa,
-                                                     Planes& pb) {
-    int first = wq - goff;
-    if (first < 0) first += totw;
-    const int lo = first * 32, step = totw * 32;
-    int mine = (lo + lane < cnt) ? __ldcg(list + lo + lane) : 0x7FFFFFFF;
-    for (int t0 = lo; t0 < cnt; t0 += step) {
-        const int nxt = (t0 + step + lane < cnt) ? __ldcg(list + t0 + step + lane) : 0x7FFFFFFF;
-#pragma unroll
-        for (int half = 0; half < 32 / PEEL_STAGE_ROWS; ++half) {
-            const bool q = (mine < rowlimit) && ((lane / PEEL_STAGE_ROWS) == half);
-            const uint32_t bal = __ballot_sync(0xFFFFFFFFu, q);
-            if (bal) {
-                if (rg.issued - rg.consumed == PEEL_STAGES) ring_consume(rg, lane, pa, pb);
-                const int st = rg.issued & (PEEL_STAGES - 1);
-                const int total = __popc(bal);
-                const int slot = __popc(bal & ((1u << lane) - 1u));
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // earlier reads of this stage are done
-                if (lane == 0) mbar_expect_tx(rg.bars + st, (uint32_t)total * 256u);
-                __syncwarp();
-                if (q) bulk_copy_256(rg.slots + st * PEEL_STAGE_WORDS + slot * PW2, pair + (size_t)mine * PW2, rg.bars + st);
-                rg.rowsp = (rg.rowsp & ~(0xFFu << (8 * st))) | ((uint32_t)total << (8 * st));
-                ++rg.issued;
-            }
-        }
-        mine = nxt;
-    }
-}
-
-// Consume everything still in flight.
-__device__ __forceinline__ void ring_drain(Ring& rg, int lane, Planes& pa, Planes& pb) {
-    while (rg.consumed < rg.issued) ring_consume(rg, lane, pa, pb);
-}
-
-// Warp 0: commit one half (panel) of the pair.
-template <bool MULTI>
-__device__ __forceinline__ void pair_commit_half(uint32_t* cp, int K, const uint32_t* delta, int pm, int lane, int J,
-                                                 int* fl_next, int* nf_next, const PeerTable& pt, int which_next,
-                                                 int* pub, uint32_t* newmask_out) {
-    if constexpr (MULTI) peel_commit_world(cp, K, delta, pm, lane, J, pt, which_next, pub, newmask_out);
-    else peel_commit(cp, K, delta, pm, lane, J, fl_next, nf_next, newmask_out);
-}
-
-template <bool MULTI>
-__global__ void __launch_bounds__(PEEL_WARPS * 32, 2)
-k_peel_persistent(const uint32_t* __restrict__ bits, const int* __restrict__ count, int* __restrict__ rank_u,
-                  int* flistA, int* flistB, Scal* scal, uint32_t* __restrict__ cplanes, const PeelItem* __restrict__ items,
-                  int slots, uint32_t* partials, unsigned int* pdone, unsigned int* pcommit, int K, int world, int rank,
-                  int planes_in_smem, PeerTable pt) {
-    int* const nf3 = scal->nf3;
-    extern __shared__ __align__(128) unsigned char peel_smem_raw[];
-    PeelShared& sh = *reinterpret_cast<PeelShared*>(peel_smem_raw);
-    uint32_t* cp_smem = reinterpret_cast<uint32_t*>(peel_smem_raw + sizeof(PeelShared));
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int G = gridDim.x, B = blockIdx.x;
-    const int U = scal->U;
-    const size_t cp_stride = (size_t)(K + 1) * PW;
-    unsigned int epoch = 0;
-    unsigned int* bar = reinterpret_cast<unsigned int*>(&scal->barrier);
-
-    // ---- init: int counts -> planes, alive mask, front 0 (stripe 0 of every pair) -----------------
-    for (int sl = 0; sl < slots; ++sl) {
-        const PeelItem it = items[(size_t)sl * G + B];
-        if (it.lp < 0 || it.stripe != 0) continue;                  // CTA-uniform
-        for (int c2 = threadIdx.x; c2 < 2 * TW; c2 += blockDim.x) {  // 32 consecutive columns per warp step
-            const int h = c2 >> 10, c = c2 & (TW - 1), l = 2 * it.lp + h;
-            const int j = panel_of_local(l, world, rank) * TW + c;
-            uint32_t* cp = planes_in_smem ? cp_smem + (2 * it.slot + h) * cp_stride : cplanes + (size_t)l * cp_stride;
-            const int v = (j < U) ? count[(size_t)l * TW + c] : 0;
-            for (int p = 0; p < K; ++p) {
-                const uint32_t w = __ballot_sync(0xFFFFFFFFu, (v >> p) & 1);
-                if (lane == 0) cp[p * PW + (c >> 5)] = w;
-            }
-            const uint32_t a = __ballot_sync(0xFFFFFFFFu, j < U);
-            if (lane == 0) cp[K * PW + (c >> 5)] = a;
-        }
-        __syncthreads();
-        if (warp < 2) {                                             // warp h publishes front 0 of panel h
-            const int h = warp, l = 2 * it.lp + h;
-            uint32_t* cp = planes_in_smem ? cp_smem + (2 * it.slot + h) * cp_stride : cplanes + (size_t)l * cp_stride;
-            pair_commit_half<MULTI>(cp, K, nullptr, 0, lane, panel_of_local(l, world, rank), flistA, &nf3[0], pt, 0,
-                                    &scal->pub3[0], sh.newmask[h]);
-        }
-        __syncthreads();
-        for (int c2 = threadIdx.x; c2 < 2 * TW; c2 += blockDim.x) {
-            const int h = c2 >> 10, c = c2 & (TW - 1);
-            if ((sh.newmask[h][c >> 5] >> (c & 31)) & 1u) rank_u[(size_t)(2 * it.lp + h) * TW + c] = 0;
-        }
-        __syncthreads();
-    }
-    int nf = MULTI ? world_barrier(scal, epoch, pt, &scal->pub3[0], 0, sh.cnt, &sh.nf)
-                   : grid_barrier(bar, epoch, &nf3[0], &sh.nf);
-
-    // ---- fronts ----------------------------------------------------------------------------------
-    Ring rg;                                                          // this warp's gather ring, for the whole kernel
-    rg.slots = &sh.ring[warp][0][0];
-    rg.bars = &sh.bars[warp][0];
-    if (lane == 0) {
-        for (int st = 0; st < PEEL_STAGES; ++st) mbar_init(rg.bars + st, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncwarp();
-    int k = 0;
-    unsigned long long t_acc = 0, t_mc = 0, t_bar = 0, t_mark = global_ns();   // thread 0's phase clock
-    for (;; ++k) {
-        if (nf <= 0) break;
-        if (B == 0 && threadIdx.x == 0) {
-            if constexpr (MULTI) scal->pub3[(k + 2) % 3] = 0;
-            else nf3[(k + 2) % 3] = 0;
-        }
-        const int* fl = (k & 1) ? flistB : flistA;
-        int* fl_next = (k & 1) ? flistA : flistB;
-        for (int sl = 0; sl < slots; ++sl) {
-            const PeelItem it = items[(size_t)sl * G + B];
-            if (it.lp < 0) continue;                                  // CTA-uniform
-            const int l0 = 2 * it.lp;
-            const int J0 = panel_of_local(l0, world, rank);           // J1 = J0 + 1
-            if (J0 * TW >= U) continue;
-            const int rowlimit = min((J0 + 2) * TW, U);               // rows stored for the pair
-            const uint32_t* pbase = bits + pair_words_before(it.lp, world, rank);
-            // stripes actually used for this front: at least 512 list entries each (a short front is
-            // cheaper in one CTA than spread over many and merged)
-            const int ns = min(it.nstripes, max(1, nf >> 9));
-            if (it.stripe >= ns) continue;                            // CTA-uniform
-            const int totw = ns * PEEL_WARPS, wq = it.stripe * PEEL_WARPS + warp;
-
-            // A pass adds at most `pass_cap` list entries (what 12 register planes per warp can hold),
-            // then merges and commits; almost always one pass per front.
-            const int pass_cap = ns * (PEEL_ROWS_PER_PASS - 32 * MAX_WORLD);
-            int pr = 0, poff = 0;                                    // multi-rank: next region / offset
-            for (int pass0 = 0; pass0 < nf;) {
-                Planes pa, pb;
-                int pass_n = 0;
-                if constexpr (!MULTI) {
-                    pass_n = min(nf - pass0, pass_cap);
-                    peel_accumulate_ring(fl + pass0, pass_n, 0, wq, totw, lane, rowlimit, pbase, rg, pa, pb);
-                } else {
-                    int budget = pass_cap, goff = 0;
-                    while (pr < pt.world && budget > 0) {
-                        const int avail = sh.cnt[pr] - poff;
-                        if (avail <= 0) { ++pr; poff = 0; continue; }
-                        const int take = min(avail, budget);
-                        peel_accumulate_ring(peer_region(pt, pt.rank, k & 1, pr) + poff, take, goff, wq, totw, lane,
-                                             rowlimit, pbase, rg, pa, pb);
-                        goff = (goff + ((take + 31) >> 5)) % totw;
-                        budget -= take; pass_n += take; poff += take;
-                    }
-                }
-                ring_drain(rg, lane, pa, pb);
-                pass0 += pass_n;
-                const int groups = ((pass_n + 31) >> 5) + (MULTI ? MAX_WORLD : 0);
-                const int per = ((groups + totw - 1) / totw) << 5;    // rows a warp can have seen
-                int rp = 1;                                          // planes a warp can have touched
-                while ((1 << rp) <= per) ++rp;
-                rp = min(rp, PEEL_RP);
-                const int pmw = min(rp + PEEL_LOG_WARPS, PEEL_PM);    // planes after the in-CTA merge
-                int pm = pmw;                                        // ... and after merging the stripes
-                if (ns > 1) { int e = 1; while ((1 << e) < ns) ++e; pm = min(pmw + e, PEEL_PM); }
-                // per-warp planes -> shared memory (only the planes that can be non-zero)
-                sh.merge[warp][0][lane] = pa.ones;   sh.merge[warp][0][PW + lane] = pb.ones;
-                sh.merge[warp][1][lane] = pa.twos;   sh.merge[warp][1][PW + lane] = pb.twos;
-                sh.merge[warp][2][lane] = pa.fours;  sh.merge[warp][2][PW + lane] = pb.fours;
-#pragma unroll
-                for (int p = 0; p < PEEL_UP; ++p)
-                    if (3 + p < pm) { sh.merge[warp][3 + p][lane] = pa.up[p]; sh.merge[warp][3 + p][PW + lane] = pb.up[p]; }
-                for (int p = PEEL_RP; p < pm; ++p) { sh.merge[warp][p][lane] = 0u; sh.merge[warp][p][PW + lane] = 0u; }
-                __syncthreads();
-                if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_acc += t - t_mark; t_mark = t; }
-                // bit-sliced tree merge: warp w += warp w + half (each lane: one word of each panel)
-                for (int half = PEEL_WARPS / 2; half >= 1; half >>= 1) {
-                    if (warp < 2 * half) {                            // warps [0, half): panel 0, [half, 2 half): panel 1
-                        const int wl = warp % half, off = (warp / half) * PW + lane;
-                        uint32_t carry = 0;
-                        for (int p = 0; p < pm; ++p) {
-                            const uint32_t a = sh.merge[wl][p][off], b2 = sh.merge[wl + half][p][off];
-                            const uint32_t x = a ^ b2;
-                            sh.merge[wl][p][off] = x ^ carry;
-                            carry = (a & b2) | (x & carry);
-                        }
-                    }
-                    __syncthreads();
-                }
-                bool commit = true;
-                unsigned int commits_before = 0;
-                if (ns > 1) {
-                    // Heavy pair shared by several CTAs: park this stripe's partial sums in global
-                    // memory; whichever stripe arrives last adds the others to its own and commits.
-                    uint32_t* mine = partials + ((size_t)B * PEEL_PM_MAX) * PW2;
-                    if (warp < 2)
-                        for (int p = 0; p < pm; ++p) __stcg(mine + p * PW2 + warp * PW + lane, sh.merge[0][p][warp * PW + lane]);
-                    __syncthreads();
-                    if (threadIdx.x == 0) {
-                        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(commits_before) : "l"(&pcommit[it.lp]) : "memory");
-                        __threadfence();
-                        const unsigned int old = atomicAdd(&pdone[it.lp], 1u);
-                        const bool last = old + 1u == (unsigned int)ns;
-                        if (last) pdone[it.lp] = 0u;                  // nobody touches it again before the next pass
-                        sh.nf = last ? 1 : 0;
-                        __threadfence();
-                    }
-                    __syncthreads();
-                    commit = sh.nf != 0;
-                    if (commit && warp < 2) {                         // warp h merges half h
-                        for (int st2 = 0; st2 < ns; ++st2) {
-                            if (st2 == it.stripe) continue;
-                            const uint32_t* other = partials + ((size_t)(B - it.stripe + st2) * PEEL_PM_MAX) * PW2 + warp * PW;
-                            uint32_t o[PEEL_PM];                      // all planes in flight at once (L2 latency)
-#pragma unroll
-                            for (int p = 0; p < PEEL_PM; ++p) o[p] = (p < pm) ? __ldcg(other + p * PW2 + lane) : 0u;
-                            uint32_t carry = 0;
-#pragma unroll
-                            for (int p = 0; p < PEEL_PM; ++p) {
-                                if (p < pm) {
-                                    const uint32_t a = sh.merge[0][p][warp * PW + lane];
-                                    const uint32_t x = a ^ o[p];
-                                    sh.merge[0][p][warp * PW + lane] = x ^ carry;
-                                    carry = (a & o[p]) | (x & carry);
-                                }
-                            }
-                        }
-                    }
-                    __syncthreads();
-                }
-                if (commit) {
-                    if (warp < 2) {                                   // warp h commits panel h of the pair
-                        const int h = warp, l = l0 + h, J = J0 + h;
-                        if (J * TW >= U) {
-                            sh.newmask[h][lane] = 0u;
-                        } else {
-                            uint32_t* cp = planes_in_smem ? cp_smem + (2 * it.slot + h) * cp_stride
-                                                          : cplanes + (size_t)l * cp_stride;
-                            pair_commit_half<MULTI>(cp, K, &sh.merge[0][0][h * PW], pm, lane, J, fl_next, &nf3[(k + 1) % 3],
-                                                    pt, (k + 1) & 1, &scal->pub3[(k + 1) % 3], sh.newmask[h]);
-                        }
-                    }
-                    __syncthreads();
-                    for (int c = threadIdx.x; c < 2 * TW; c += blockDim.x) {
-                        const int h = c >> 10, cc = c & (TW - 1);
-                        if ((sh.newmask[h][cc >> 5] >> (cc & 31)) & 1u) rank_u[(size_t)(l0 + h) * TW + cc] = k + 1;
-                    }
-                }
-                __syncthreads();
-                if (ns > 1) {
-                    // A further pass of the same front may only start (and overwrite the parked
-                    // partial sums) once this pass has been committed.
-                    if (threadIdx.x == 0) {
-                        if (commit) { __threadfence(); atomicAdd(&pcommit[it.lp], 1u); }
-                        if (pass0 < nf) {
-                            unsigned int v;
-                            do {
-                                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&pcommit[it.lp]) : "memory");
-                            } while (v == commits_before);
-                        }
-                    }
-                    __syncthreads();
-                }
-                if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_mc += t - t_mark; t_mark = t; }
-            }
-        }
-        nf = MULTI ? world_barrier(scal, epoch, pt, &scal->pub3[(k + 1) % 3], (k + 1) & 1, sh.cnt, &sh.nf)
-                   : grid_barrier(bar, epoch, &nf3[(k + 1) % 3], &sh.nf);
-        if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_bar += t - t_mark; t_mark = t; }
-    }
-    if (B == 0 && threadIdx.x == 0) scal->fronts = (nf < 0) ? -1 : k;
-    if (threadIdx.x == 0 && (B == 0 || B == G - 1)) {                 // CTA 0 owns the heaviest pairs
-        unsigned long long* d = scal->dbg + (B == 0 ? 0 : 4);
-        d[0] = t_acc; d[1] = t_mc; d[2] = t_bar; d[3] = (unsigned long long)k;
-    }
-}
 
 // ------------------------------------------------------------------------------------------------
 // Single-GPU peel with per-front load balancing.
@@ -1598,10 +1031,12 @@ __device__ __forceinline__ void peel_accumulate_groups(const int* pre, int npre,
 
 // One warp: subtract a bit-sliced delta (plane p of this lane's word = delta(p), p < pm; pm = 0: none)
 // from panel J's count planes in global memory, retire the columns that reached zero, write their
-// rank and append them, in column order, as panel J's segment of the next front.
-template <class Delta>
+// rank and append them, in column order, as panel J's segment of the next front.  MULTI: the segment
+// and its size go into every rank's replica of the front (plain stores to peer-mapped memory, posted
+// over NVLink; the barrier that follows fences them).
+template <bool MULTI, class Delta>
 __device__ __forceinline__ void peel_commit_seg(uint32_t* cp, int K, Delta delta, int pm, int lane, int J, int* seg_next,
-                                                int* cnt_next, int* rank_panel, int rank_value) {
+                                                int* cnt_next, int* rank_panel, int rank_value, const PeerTable& pt) {
     uint32_t c[PEEL_KMAX];
 #pragma unroll
     for (int p = 0; p < PEEL_KMAX; ++p) c[p] = (p < K) ? __ldcg(cp + p * PW + lane) : 0u;   // all planes in flight at once
@@ -1627,10 +1062,33 @@ __device__ __forceinline__ void peel_commit_seg(uint32_t* cp, int K, Delta delta
         const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
         if (lane >= o) incl += t;
     }
-    if (lane == 31 && incl) __stcg(cnt_next, incl);          // (the slot was cleared two fronts ago)
     int* dst = seg_next + (size_t)J * TW + (incl - cnt);
+    if (lane == 31 && incl) __stcg(cnt_next, incl);          // (the slot was cleared two fronts ago)
     uint32_t w = nw;
     const int c0 = lane * 32;
+    if constexpr (MULTI) {
+        if (pt.world > 1) {
+            const char* mine = pt.base[pt.rank];
+            const size_t coff = reinterpret_cast<const char*>(cnt_next) - mine;
+            const size_t soff = reinterpret_cast<const char*>(dst) - mine;
+            if (lane == 31 && incl) {
+                for (int r = 0; r < pt.world; ++r)
+                    if (r != pt.rank) *reinterpret_cast<volatile int*>(pt.base[r] + coff) = incl;
+            }
+            int q = 0;
+            while (w) {
+                const int b = __ffs(w) - 1;
+                w &= w - 1;
+                const int v = J * TW + c0 + b;
+                __stcg(dst + q, v);
+                for (int r = 0; r < pt.world; ++r)
+                    if (r != pt.rank) reinterpret_cast<volatile int*>(pt.base[r] + soff)[q] = v;
+                rank_panel[c0 + b] = rank_value;
+                ++q;
+            }
+            return;
+        }
+    }
     while (w) {
         const int b = __ffs(w) - 1;
         w &= w - 1;
@@ -1667,92 +1125,64 @@ __device__ __forceinline__ int pair_fixed_cost(int total) {      // total = grou
     return total <= PEEL_WARP_PAIR_GROUPS + PEEL_COST_WARP_PAIR ? PEEL_COST_WARP_PAIR : PEEL_COST_CTA_PAIR;
 }
 
-// Barrier over all CTAs of all ranks for the load-balanced kernel, carrying the front exchange.  The
-// committers have written this rank's panels of the coming front (segments + counts) into the rank's
-// OWN copy; once every local CTA has arrived, CTA 0 copies them into every peer's copy (posted stores
-// over NVLink), fences once at system scope, sends one message per peer, waits for every peer's
-// message and releases the local CTAs.  Returns 0, or -1 after a time-out (everybody leaves).
-__device__ __forceinline__ int world_barrier_seg(Scal* scal, unsigned int& epoch, const PeerTable& pt, int* cnt_next,
-                                                 int* seg_next, int nq_local, int npan, int* flag_smem) {
+// Barrier over all CTAs of all ranks.  The front exchange itself is already under way when a CTA gets
+// here: committers wrote their panels' new members into every rank's replica.  Each CTA makes its own
+// pushes visible system-wide (one thread fences after the CTA barrier: the fence is cumulative over
+// it), then arrives on the local counter; whoever arrives last on this GPU sends the epoch to every
+// rank.  Every CTA polls the `world` message words of its own rank - nobody relays a release.  Critical
+// path: slowest CTA's fence + arrive -> one NVLink store -> poll -> acquire fence.
+// Returns 0, or -1 after a time-out or a protocol error (every CTA of every rank then leaves).
+// dbg (CTA 0, thread 0): bdbg[0] += fence + arrive, bdbg[1] += waiting for the messages, bdbg[2] += acquire fence.
+__device__ __forceinline__ int world_barrier_seg(Scal* scal, unsigned int& epoch, unsigned int ebase, const PeerTable& pt,
+                                                 int* flag_smem) {
     __syncthreads();
     ++epoch;
+    const unsigned int gepoch = ebase + epoch;                                   // epoch across launches
     const unsigned long long t0 = global_ns();
-    unsigned long long tb = t0, tn;
-    if (threadIdx.x == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(&scal->barrier) : "memory");
-    if (blockIdx.x == 0) {
-        if (threadIdx.x == 0) {
-            unsigned int v;
-            do {                                                      // every local CTA has arrived
-                asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&scal->barrier) : "memory");
-            } while (v < epoch * gridDim.x);
-            asm volatile("fence.acq_rel.gpu;" ::: "memory");
-            tn = global_ns(); scal->bdbg[1] += tn - tb; tb = tn;
-        }
-        __syncthreads();
-        if (pt.world > 1) {
-            const char* mybase = pt.base[pt.rank];
-            const size_t coff = reinterpret_cast<const char*>(cnt_next) - mybase;
-            const size_t soff = reinterpret_cast<const char*>(seg_next) - mybase;
-            for (int t = threadIdx.x; t < 2 * nq_local; t += blockDim.x) {       // one local panel per thread
-                const int J = 2 * ((t >> 1) * pt.world + pt.rank) + (t & 1);
-                if (J >= npan) continue;
-                const int c = __ldcg(cnt_next + J);
-                if (c <= 0) continue;
-                for (int r = 0; r < pt.world; ++r) {
-                    if (r == pt.rank) continue;
-                    int* pc = reinterpret_cast<int*>(pt.base[r] + coff);
-                    int* ps = reinterpret_cast<int*>(pt.base[r] + soff) + (size_t)J * TW;
-                    for (int i = 0; i < c; ++i) ps[i] = __ldcg(seg_next + (size_t)J * TW + i);
-                    pc[J] = c;
-                }
-            }
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            PeerState* me = peer_state(pt, pt.rank);
-            bool dead = false;
-            tn = global_ns(); scal->bdbg[2] += tn - tb; tb = tn;
-            __threadfence_system();                                   // the pushes are visible before the message
-            const unsigned long long msg = (unsigned long long)epoch << 32;
-            for (int r = 0; r < pt.world; ++r)
-                asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(&peer_state(pt, r)->xmsg[pt.rank]), "l"(msg)
-                             : "memory");
-            tn = global_ns(); scal->bdbg[3] += tn - tb; tb = tn;
-            for (int r = 0; r < pt.world && !dead; ++r) {             // wait for every rank's message
-                unsigned long long m;
-                do {
-                    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(m) : "l"(&me->xmsg[r]) : "memory");
-                    if ((unsigned int)(m >> 32) >= epoch) break;
-                    int ab;
-                    asm volatile("ld.relaxed.sys.global.s32 %0, [%1];" : "=r"(ab) : "l"(&me->abort) : "memory");
-                    if (ab || global_ns() - t0 > PEER_TIMEOUT_NS) dead = true;
-                } while (!dead);
-            }
-            tn = global_ns(); scal->bdbg[4] += tn - tb; tb = tn;
-            __threadfence_system();                                   // acquire: peers' pushes are visible
-            tn = global_ns(); scal->bdbg[5] += tn - tb; tb = tn;
-            if (dead) {
-                for (int r = 0; r < pt.world; ++r)
-                    asm volatile("st.relaxed.sys.global.s32 [%0], %1;" ::"l"(&peer_state(pt, r)->abort), "r"(1) : "memory");
-            }
-            scal->xtotal = dead ? -1 : 0;
-            __threadfence();
-            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&scal->go), "r"(epoch) : "memory");
-            tn = global_ns(); scal->bdbg[6] += tn - tb; tb = tn;
-        }
-    }
     if (threadIdx.x == 0) {
-        bool dead = false;
-        if (blockIdx.x != 0) {
-            unsigned int v;
-            do {
-                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&scal->go) : "memory");
-            } while (v < epoch && global_ns() - t0 < 2 * PEER_TIMEOUT_NS);
-            if (v < epoch) dead = true;
+        *flag_smem = 0;
+        if (pt.world > 1) asm volatile("fence.acq_rel.sys;" ::: "memory");       // this CTA's pushes are performed
+        unsigned int old;
+        asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(old) : "l"(&scal->barrier) : "memory");
+        if (old + 1u == epoch * gridDim.x) {                                     // last CTA of this GPU to arrive
+            asm volatile("fence.acq_rel.sys;" ::: "memory");                      // ... cumulative over the others' releases
+            const unsigned long long msg = (unsigned long long)gepoch << 32;
+            for (int r = 0; r < pt.world; ++r)
+                asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(&peer_state(pt, r)->xmsg[gepoch & 1u][pt.rank]),
+                             "l"(msg)
+                             : "memory");
         }
-        int total;
-        asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(total) : "l"(&scal->xtotal) : "memory");
-        *flag_smem = (dead || total < 0) ? -1 : 0;
+        if (blockIdx.x == 0) scal->bdbg[0] += global_ns() - t0;
+    }
+    __syncthreads();
+    if (threadIdx.x < pt.world) {
+        PeerState* me = peer_state(pt, pt.rank);
+        const unsigned long long* word = &me->xmsg[gepoch & 1u][threadIdx.x];
+        bool dead = false;
+        unsigned int spins = 0;
+        for (;;) {
+            unsigned long long m;
+            asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(m) : "l"(word) : "memory");
+            const unsigned int e = (unsigned int)(m >> 32);
+            if (e == gepoch) break;
+            if ((int)(e - gepoch) > 0) { dead = true; break; }                   // a peer is two barriers ahead: protocol error
+            if ((++spins & 63u) == 0u) {
+                int ab;
+                asm volatile("ld.relaxed.sys.global.s32 %0, [%1];" : "=r"(ab) : "l"(&me->abort) : "memory");
+                if (ab || global_ns() - t0 > PEER_TIMEOUT_NS) { dead = true; break; }
+            }
+        }
+        if (dead) {
+            for (int r = 0; r < pt.world; ++r)
+                asm volatile("st.relaxed.sys.global.s32 [%0], %1;" ::"l"(&peer_state(pt, r)->abort), "r"(1) : "memory");
+            *flag_smem = -1;
+        }
+        const unsigned long long t1 = global_ns();
+        asm volatile("fence.acq_rel.sys;" ::: "memory");                          // acquire: the peers' pushes are visible
+        if (blockIdx.x == 0 && threadIdx.x == 0) {
+            scal->bdbg[1] += t1 - t0;
+            scal->bdbg[2] += global_ns() - t1;
+        }
     }
     __syncthreads();
     return *flag_smem;
@@ -1796,7 +1226,8 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
     int* pre = reinterpret_cast<int*>(peel_smem_raw + sizeof(DynShared));   // [npan + 1]
     int* S = pre + npan + 1;                                        // [nq + 1] cost units before local pair lp
     const size_t cp_stride = (size_t)(K + 1) * PW;
-    unsigned int epoch = 0;
+    unsigned int epoch = 0, ebase = 0;
+    if constexpr (MULTI) ebase = peer_state(pt, pt.rank)->epoch_base;
     unsigned int* bar = reinterpret_cast<unsigned int*>(&scal->barrier);
 
     // ---- init: int counts -> planes, alive mask, front 0 ------------------------------------------
@@ -1818,13 +1249,13 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
         if (warp < 2) {
             const int J = 2 * Q + warp, l = 2 * lp + warp;
             if (J < npan)
-                peel_commit_seg(cplanes + (size_t)l * cp_stride, K, NoDelta{}, 0, lane, J, segA, pcnt + J,
-                                rank_u + (size_t)l * TW, 0);
+                peel_commit_seg<MULTI>(cplanes + (size_t)l * cp_stride, K, NoDelta{}, 0, lane, J, segA, pcnt + J,
+                                       rank_u + (size_t)l * TW, 0, pt);
         }
         __syncthreads();
     }
     if constexpr (MULTI) {
-        if (world_barrier_seg(scal, epoch, pt, pcnt, segA, nq, npan, &sh.nf) < 0) {
+        if (world_barrier_seg(scal, epoch, ebase, pt, &sh.nf) < 0) {
             if (B == 0 && threadIdx.x == 0) scal->fronts = -1;
             return;
         }
@@ -1952,8 +1383,8 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
                 for (int h = 0; h < 2; ++h) {
                     const int J = 2 * Q + h, l = 2 * lp + h;
                     if (J < npan)
-                        peel_commit_seg(cplanes + (size_t)l * cp_stride, K, SmemDelta{&sh.merge[warp][0][h * PW + lane]}, pm,
-                                        lane, J, seg_next, cnt_next + J, rank_u + (size_t)l * TW, k + 1);
+                        peel_commit_seg<MULTI>(cplanes + (size_t)l * cp_stride, K, SmemDelta{&sh.merge[warp][0][h * PW + lane]},
+                                               pm, lane, J, seg_next, cnt_next + J, rank_u + (size_t)l * TW, k + 1, pt);
                 }
                 __syncwarp();
             }
@@ -2067,20 +1498,27 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
                 if (commit && warp < 2) {
                     const int J = 2 * Q + warp, l = 2 * lp + warp;
                     if (J < npan)
-                        peel_commit_seg(cplanes + (size_t)l * cp_stride, K,
-                                        SmemDelta{direct ? &sh.merge[0][0][warp * PW + lane] : &acc[0][warp * PW + lane]},
-                                        direct ? pm_last : pq, lane, J, seg_next, cnt_next + J, rank_u + (size_t)l * TW, k + 1);
+                        peel_commit_seg<MULTI>(cplanes + (size_t)l * cp_stride, K,
+                                               SmemDelta{direct ? &sh.merge[0][0][warp * PW + lane] : &acc[0][warp * PW + lane]},
+                                               direct ? pm_last : pq, lane, J, seg_next, cnt_next + J, rank_u + (size_t)l * TW,
+                                               k + 1, pt);
                 }
                 __syncthreads();
                 if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_mc += t - t_mark; t_mark = t; }
             }
         }
         if constexpr (MULTI) {
-            if (world_barrier_seg(scal, epoch, pt, cnt_next, seg_next, nq, npan, &sh.nf) < 0) { k = -1; break; }
+            if (world_barrier_seg(scal, epoch, ebase, pt, &sh.nf) < 0) { k = -1; break; }
         } else {
             grid_barrier_plain(bar, epoch);
         }
         if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_bar += t - t_mark; t_mark = t; }
+    }
+    if constexpr (MULTI) {
+        // Exit barrier: once past it, no CTA of any rank reads this launch's front replica any more, so
+        // the next launch may push its front 0 without any host-level hand-shake.
+        if (k >= 0 && world_barrier_seg(scal, epoch, ebase, pt, &sh.nf) < 0) k = -1;
+        if (B == 0 && threadIdx.x == 0) peer_state(pt, pt.rank)->epoch_base = ebase + epoch;
     }
     if (B == 0 && threadIdx.x == 0) scal->fronts = k;
     if (threadIdx.x == 0 && (B == 0 || B == G - 1)) {
@@ -2252,161 +1690,70 @@ static int apply(const Plan& P, int k, const uint32_t* masks, int* any_out, cuda
 }
 
 
-// Launch the persistent peel.  peers == nullptr: single rank.  Otherwise the fused multi-rank kernel
-// with the peer buffers.  Leaves the front count in scal->fronts (-1 after a time-out).
-//
-// Work assignment (host, per call): with at least as many panels as CTAs every panel is one item
-// and the items are dealt boustrophedon, heaviest first, so the triangular panel sizes balance.
-// With fewer panels than CTAs the spare CTAs go to the heaviest panels as extra row stripes
-// (one SM gathers at most ~226 random 128-byte rows per microsecond, see profiles/): stripes of a
-// panel sit in consecutive CTAs and the last one to arrive merges and commits.
-// Peer-mapped buffer of the load-balanced fused peel: [PeerState | counts 3 x stride | pad | segments A | segments B]
+// Peer-mapped buffer of the fused multi-rank peel: [PeerState | counts 3 x stride | pad | segments A | segments B]
 static int peer_cnt_stride(const Layout& L) { return L.np + 2; }
 static size_t peer_seg_offset(const Layout& L) {
     return align_up(sizeof(PeerState) + sizeof(int) * 3 * (size_t)(L.np + 2), 256);
 }
 
+static size_t peel_smem_bytes(const Layout& L) {
+    return sizeof(DynShared) + sizeof(int) * (size_t)(L.np + 1 + L.npl / 2 + 2);
+}
+// The persistent kernel keeps two per-front tables in shared memory (one entry per panel / per local
+// pair) and scans the panel counts with DYN_MAX_PPT pairs per thread: populations beyond that (N > 2M)
+// take the one-front-per-launch path.
+static bool persistent_peel_fits(const Layout& L) {
+    return L.kplanes <= PEEL_KMAX && peel_smem_bytes(L) <= 227 * 1024 &&
+           (L.np + 1) / 2 <= DYN_MAX_PPT * PEEL_WARPS * 32;
+}
+
+// Launch the persistent peel.  peers == nullptr: single rank.  Otherwise the fused multi-rank kernel
+// with the peer buffers.  Leaves the front count in scal->fronts (-1 after a time-out).
 static int peel_persistent(const Plan& P, cudaStream_t s, const PeerTable* peers = nullptr) {
     const Layout& L = P.L;
+    EVX_REQUIRE(persistent_peel_fits(L), EVX_ERR_ARG, "persistent peel: population of %lld rows exceeds the kernel's tables",
+                (long long)L.n);
     int dev = 0, sms = 0, per_sm = 0;
     EVX_CUDA(cudaGetDevice(&dev));
     EVX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    const size_t base_smem = sizeof(PeelShared);
-    const void* kernel = peers ? (const void*)k_peel_persistent<true> : (const void*)k_peel_persistent<false>;
-    const size_t cp_bytes = sizeof(uint32_t) * (size_t)(L.kplanes + 1) * PW;
-    EVX_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(base_smem + 16 * 1024)));
-    EVX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, PEEL_WARPS * 32, base_smem + 16 * 1024));
-    EVX_REQUIRE(per_sm >= 1, EVX_ERR_CUDA, "persistent peel kernel does not fit on an SM");
-    int grid = sms * per_sm;
-    if (grid > PEEL_MAX_GRID) grid = PEEL_MAX_GRID;
     const int nlp = L.npl / 2;                                     // local pairs
-    const int npl = nlp > 0 ? nlp : 1;
-
-    // One GPU: the load-balanced kernel, unless it cannot hold its tables (or EVX_PEEL=static asks for the other).
-    {
-        const char* e = getenv("EVX_PEEL");
-        const int npairs_g = (L.np + 1) / 2;
-        const size_t dyn_smem = sizeof(DynShared) + sizeof(int) * (size_t)(L.np + 1 + nlp + 2);
-        // Fused multi-rank peel: the fixed-ownership kernel below stays the default - with the per-front
-        // world barrier dominating, the balanced kernel measured slower on 4 GPUs (21.2 vs 18.3 ms at N = 1M,
-        // equal on 2); EVX_PEEL=balanced selects it.
-        const bool want = peers ? (e && strcmp(e, "balanced") == 0) : !(e && strcmp(e, "static") == 0);
-        if (want && L.kplanes <= PEEL_KMAX && dyn_smem <= 113 * 1024 && npairs_g <= DYN_MAX_PPT * PEEL_WARPS * 32) {
-            const void* dk = peers ? (const void*)k_peel_dynamic<true> : (const void*)k_peel_dynamic<false>;
-            EVX_CUDA(cudaFuncSetAttribute(dk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_smem));
-            EVX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dk, PEEL_WARPS * 32, dyn_smem));
-            EVX_REQUIRE(per_sm >= 1, EVX_ERR_CUDA, "load-balanced peel kernel does not fit on an SM");
-            int dgrid = sms * per_sm;
-            if (dgrid > PEEL_MAX_GRID) dgrid = PEEL_MAX_GRID;
-            const int useful = 16 * (nlp > 0 ? nlp : 1);            // a small population cannot feed every CTA:
-            if (dgrid > useful) dgrid = useful < 32 ? 32 : useful;  // fewer arrivals per grid barrier
-            EVX_CUDA(cudaMemsetAsync(P.at<unsigned int>(L.pdone), 0, sizeof(unsigned int) * 2 * (size_t)L.npl_max, s));
-            const uint32_t* bits = P.at<uint32_t>(L.bits);
-            const int* count = P.at<int>(L.count);
-            int* rank_u = P.at<int>(L.rank_u);
-            Scal* scal = P.at<Scal>(L.scal);
-            uint32_t* cpl = P.at<uint32_t>(L.cplanes);
-            uint32_t* partials = P.at<uint32_t>(L.partials);
-            unsigned int* pdone = P.at<unsigned int>(L.pdone);
-            int K = L.kplanes, ps = peer_cnt_stride(L), world = L.world, rank = L.rank;
-            int *pcnt, *fa, *fb;
-            PeerTable pt{};
-            if (peers) {
-                // front segments and per-panel counts live in the peer-mapped buffer (every rank holds all panels);
-                // evx_nds_shard_peer_init has cleared the counts
-                pt = *peers;
-                char* mine = pt.base[L.rank];
-                pcnt = reinterpret_cast<int*>(mine + sizeof(PeerState));
-                fa = reinterpret_cast<int*>(mine + peer_seg_offset(L));
-                fb = fa + L.npad;
-            } else {
-                pcnt = P.at<int>(L.pcnt);
-                fa = P.at<int>(L.flist);
-                fb = P.at<int>(L.flist2);
-                EVX_CUDA(cudaMemsetAsync(pcnt, 0, sizeof(int) * 3 * (size_t)ps, s));
-            }
-            void* args[] = {&bits, &count, &rank_u, &fa, &fb, &scal, &cpl, &pcnt, &ps, &partials, &pdone, &K, &world, &rank, &pt};
-            EVX_CUDA(cudaLaunchCooperativeKernel(dk, dim3(dgrid), dim3(PEEL_WARPS * 32), args, dyn_smem, s));
-            ++evx::launch_counter();
-            return EVX_OK;
-        }
-    }
-
-    // item table: items[slot * grid + cta]
-    std::vector<PeelItem> items;
-    int slots = 1, planes_in_smem = 0;
-    if (nlp >= grid) {
-        slots = (int)ceil_div(nlp, grid);
-        items.assign((size_t)slots * grid, PeelItem{-1, 0, 1, 0});
-        for (int q = 0; q < nlp; ++q) {
-            const int slot = q / grid, r = q % grid;
-            const int cta = (slot & 1) ? (grid - 1 - r) : r;
-            items[(size_t)slot * grid + cta] = PeelItem{nlp - 1 - q, 0, 1, slot};         // heaviest first
-        }
-        planes_in_smem = ((size_t)slots * 2 * cp_bytes <= 16 * 1024) ? 1 : 0;
-    } else {
-        // weights ~ rows a panel can see; stripes proportional to weight, every panel at least one
-        std::vector<int> st(npl, 1);
-        double wsum = 0;
-        for (int l = 0; l < npl; ++l) wsum += (double)(l * L.world + L.rank + 1);
-        int used = 0;
-        for (int l = 0; l < npl; ++l) {
-            int v = (int)((double)grid * (l * L.world + L.rank + 1) / wsum);
-            const int by_rows = (int)ceil_div((int64_t)(l * L.world + L.rank + 1) * 2 * TW, 32768);   // >= 32k potential rows each
-            if (v > by_rows) v = by_rows;
-            st[l] = v < 1 ? 1 : (v > PEEL_MAX_STRIPES ? PEEL_MAX_STRIPES : v);
-            used += st[l];
-        }
-        while (used > grid) {                                       // rounding overshoot: trim the lightest
-            for (int l = 0; l < npl && used > grid; ++l)
-                if (st[l] > 1) { --st[l]; --used; }
-        }
-        auto cap = [&](int l) {
-            const int by_rows = (int)ceil_div((int64_t)(l * L.world + L.rank + 1) * 2 * TW, 32768);
-            return by_rows < PEEL_MAX_STRIPES ? by_rows : PEEL_MAX_STRIPES;
-        };
-        for (int l = npl - 1; used < grid;) {                        // spare CTAs: heaviest panels first
-            if (st[l] < cap(l)) { ++st[l]; ++used; }
-            if (--l < 0) {
-                l = npl - 1;
-                bool room = false;
-                for (int t = 0; t < npl; ++t) room |= st[t] < cap(t);
-                if (!room) break;
-            }
-        }
-        grid = used;
-        items.assign((size_t)grid, PeelItem{-1, 0, 1, 0});
-        int cta = 0;
-        for (int l = npl - 1; l >= 0; --l)
-            for (int t = 0; t < st[l]; ++t) items[cta++] = PeelItem{l, t, st[l], 0};
-        bool split = false;
-        for (int l = 0; l < npl; ++l) split |= st[l] > 1;
-        planes_in_smem = (!split && 2 * cp_bytes <= 16 * 1024) ? 1 : 0;
-        if (nlp == 0) items.assign(1, PeelItem{-1, 0, 1, 0});
-    }
-    const size_t smem = base_smem + (planes_in_smem ? (size_t)slots * 2 * cp_bytes : 0);
-    EVX_CUDA(cudaMemcpyAsync(P.at<PeelItem>(L.items), items.data(), sizeof(PeelItem) * items.size(),
-                             cudaMemcpyHostToDevice, s));
-    EVX_CUDA(cudaStreamSynchronize(s));                              // `items` is a pageable host buffer
-    EVX_CUDA(cudaMemsetAsync(P.at<unsigned int>(L.pdone), 0, sizeof(unsigned int) * 2 * (size_t)L.npl_max, s));
-
+    const size_t dyn_smem = peel_smem_bytes(L);
+    const void* dk = peers ? (const void*)k_peel_dynamic<true> : (const void*)k_peel_dynamic<false>;
+    EVX_CUDA(cudaFuncSetAttribute(dk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_smem));
+    EVX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dk, PEEL_WARPS * 32, dyn_smem));
+    EVX_REQUIRE(per_sm >= 1, EVX_ERR_CUDA, "peel kernel does not fit on an SM");
+    const int resident = sms * per_sm;                             // co-resident CTAs: the cooperative launch limit
+    int dgrid = resident < PEEL_MAX_GRID ? resident : PEEL_MAX_GRID;
+    int useful = 16 * (nlp > 0 ? nlp : 1);                          // a small population cannot feed every CTA:
+    if (useful < 32) useful = 32;                                   // fewer arrivals per grid barrier
+    if (dgrid > useful) dgrid = useful;                             // (never above `resident`)
+    EVX_CUDA(cudaMemsetAsync(P.at<unsigned int>(L.pdone), 0, sizeof(unsigned int) * (size_t)L.npl_max, s));
     const uint32_t* bits = P.at<uint32_t>(L.bits);
     const int* count = P.at<int>(L.count);
     int* rank_u = P.at<int>(L.rank_u);
-    int* fa = P.at<int>(L.flist);
-    int* fb = P.at<int>(L.flist2);
     Scal* scal = P.at<Scal>(L.scal);
     uint32_t* cpl = P.at<uint32_t>(L.cplanes);
-    const PeelItem* ditems = P.at<PeelItem>(L.items);
     uint32_t* partials = P.at<uint32_t>(L.partials);
     unsigned int* pdone = P.at<unsigned int>(L.pdone);
-    unsigned int* pcommit = pdone + L.npl_max;
-    int K = L.kplanes, world = L.world, rank = L.rank;
+    int K = L.kplanes, ps = peer_cnt_stride(L), world = L.world, rank = L.rank;
+    int *pcnt, *fa, *fb;
     PeerTable pt{};
-    if (peers) pt = *peers;
-    void* args[] = {&bits, &count, &rank_u, &fa, &fb, &scal, &cpl, &ditems, &slots, &partials, &pdone, &pcommit, &K, &world,
-                    &rank, &planes_in_smem, &pt};
-    EVX_CUDA(cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3(PEEL_WARPS * 32), args, smem, s));
+    if (peers) {
+        // front segments and per-panel counts live in the peer-mapped buffer (every rank holds all panels);
+        // evx_nds_shard_peer_init cleared it once and every launch leaves the counts cleared
+        pt = *peers;
+        char* mine = pt.base[L.rank];
+        pcnt = reinterpret_cast<int*>(mine + sizeof(PeerState));
+        fa = reinterpret_cast<int*>(mine + peer_seg_offset(L));
+        fb = fa + L.npad;
+    } else {
+        pcnt = P.at<int>(L.pcnt);
+        fa = P.at<int>(L.flist);
+        fb = P.at<int>(L.flist2);
+        EVX_CUDA(cudaMemsetAsync(pcnt, 0, sizeof(int) * 3 * (size_t)ps, s));
+    }
+    void* args[] = {&bits, &count, &rank_u, &fa, &fb, &scal, &cpl, &pcnt, &ps, &partials, &pdone, &K, &world, &rank, &pt};
+    EVX_CUDA(cudaLaunchCooperativeKernel(dk, dim3(dgrid), dim3(PEEL_WARPS * 32), args, dyn_smem, s));
     ++evx::launch_counter();
     return EVX_OK;
 }
@@ -2416,7 +1763,34 @@ static bool use_stepwise_peel() {
     return e && strcmp(e, "stepwise") == 0;
 }
 
-static thread_local int32_t g_last_fronts = 0;
+// Number of fronts of the last call, fetched lazily: the call enqueues a copy of the device-side front
+// count into a pinned host word and records an event; evx_nds_last_num_fronts() waits for that event.
+// The call itself never blocks the host.
+struct FrontCount {
+    int32_t value = 0;          // last known value
+    int32_t* pinned = nullptr;  // one pinned word per host thread (allocated on first use)
+    cudaEvent_t ev = nullptr;
+    bool pending = false;
+};
+static thread_local FrontCount g_fc;
+
+static int front_count_post(const int* dev_word, cudaStream_t s) {
+    FrontCount& fc = g_fc;
+    fc.pending = false;
+    fc.value = -1;
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &cap) != cudaSuccess) { cudaGetLastError(); return EVX_OK; }
+    if (cap != cudaStreamCaptureStatusNone) return EVX_OK;           // inside a graph capture: count not reported
+    if (!fc.pinned) {
+        EVX_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&fc.pinned), sizeof(int32_t), cudaHostAllocDefault));
+        EVX_CUDA(cudaEventCreateWithFlags(&fc.ev, cudaEventDisableTiming));
+    }
+    EVX_CUDA(cudaMemcpyAsync(fc.pinned, dev_word, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    EVX_CUDA(cudaEventRecord(fc.ev, s));
+    fc.pending = true;
+    return EVX_OK;
+}
+static void front_count_set(int32_t v) { g_fc.pending = false; g_fc.value = v; }
 
 // Optional per-stage timing (CUDA events on the caller's stream) for bench.py's roofline line.
 struct Prof {
@@ -2488,14 +1862,13 @@ extern "C" int evx_nds_shard_ranks(evx_nds_shard* p, int32_t* rank_partial, void
 extern "C" size_t evx_nds_shard_peer_bytes(const evx_nds_shard* p) {
     if (!p) return 0;
     const Layout& L = p->P.L;
-    const size_t lists = sizeof(PeerState) + 2 * sizeof(int) * (size_t)L.world * ((size_t)L.npl_max * TW);   // EVX_PEEL=static
-    const size_t segs = peer_seg_offset(L) + 2 * sizeof(int) * (size_t)L.npad;
-    return lists > segs ? lists : segs;
+    return peer_seg_offset(L) + 2 * sizeof(int) * (size_t)L.npad;
 }
 
 extern "C" int evx_nds_shard_peer_init(evx_nds_shard* p, void* local_peer_buf, void* stream) {
     EVX_REQUIRE(p && local_peer_buf, EVX_ERR_ARG, "evx_nds_shard_peer_init: null argument");
-    EVX_CUDA(cudaMemsetAsync(local_peer_buf, 0, peer_seg_offset(p->P.L), (cudaStream_t)stream));   // state + per-panel counts
+    // message words, epoch base and per-panel counts; segments need no clearing (the counts bound every read)
+    EVX_CUDA(cudaMemsetAsync(local_peer_buf, 0, peer_seg_offset(p->P.L), (cudaStream_t)stream));
     return EVX_OK;
 }
 
@@ -2510,17 +1883,23 @@ extern "C" int evx_nds_shard_peel_fused(evx_nds_shard* p, void* const* peer_bufs
         EVX_REQUIRE(peer_bufs[r], EVX_ERR_ARG, "evx_nds_shard_peel_fused: peer buffer %d is null", r);
         pt.base[r] = reinterpret_cast<char*>(peer_bufs[r]);
     }
-    pt.world = L.world; pt.rank = L.rank; pt.cap = (int64_t)L.npl_max * TW;
+    pt.world = L.world; pt.rank = L.rank;
     cudaStream_t s = (cudaStream_t)stream;
+    EVX_REQUIRE(persistent_peel_fits(L), EVX_ERR_ARG,
+                "evx_nds_shard_peel_fused: n=%lld exceeds the fused kernel's tables; use the detect / all-gather / apply loop",
+                (long long)L.n);
     int rc = peel_persistent(p->P, s, &pt);
     if (rc) return rc;
-    int fronts = 0;
     Scal* scal = p->P.at<Scal>(L.scal);
+    if (!num_fronts) return front_count_post(&scal->fronts, s);      // asynchronous: evx_nds_last_num_fronts() reads it lazily
+    int fronts = 0;
     EVX_CUDA(cudaMemcpyAsync(&fronts, &scal->fronts, sizeof(int), cudaMemcpyDeviceToHost, s));
     EVX_CUDA(cudaStreamSynchronize(s));
-    EVX_REQUIRE(fronts >= 0, EVX_ERR_CUDA, "evx_nds_shard_peel_fused: a peer did not reach the barrier within 4 s");
-    if (num_fronts) *num_fronts = fronts;
-    g_last_fronts = fronts;
+    EVX_REQUIRE(fronts >= 0, EVX_ERR_CUDA,
+                "evx_nds_shard_peel_fused: a peer did not reach the barrier within 4 s (call evx_nds_shard_peer_init on every "
+                "rank again before the next attempt)");
+    *num_fronts = fronts;
+    front_count_set(fronts);
     return EVX_OK;
 }
 
@@ -2537,13 +1916,21 @@ extern "C" int evx_debug_peel_times(evx_nds_shard* p, uint64_t* out8) {
     return EVX_OK;
 }
 
-extern "C" int32_t evx_nds_last_num_fronts(void) { return g_last_fronts; }
+extern "C" int32_t evx_nds_last_num_fronts(void) {
+    FrontCount& fc = g_fc;
+    if (fc.pending) {
+        fc.pending = false;
+        if (cudaEventSynchronize(fc.ev) == cudaSuccess) fc.value = *fc.pinned;
+        else cudaGetLastError();
+    }
+    return fc.value;
+}
 
 extern "C" int evx_nds_f32(const float* x, int64_t n, int32_t m, int32_t* rank, void* ws, size_t ws_bytes,
                            void* stream) {
     EVX_REQUIRE(n >= 0 && m >= 1 && m <= EVX_MAX_OBJECTIVES, EVX_ERR_ARG, "evx_nds_f32: bad shape n=%lld m=%d",
                 (long long)n, m);
-    g_last_fronts = 0;
+    front_count_set(0);
     if (n == 0) return EVX_OK;
     EVX_REQUIRE(x && rank, EVX_ERR_ARG, "evx_nds_f32: null pointer");
     const size_t need = evx_nds_workspace_bytes(n, m);
@@ -2553,20 +1940,16 @@ extern "C" int evx_nds_f32(const float* x, int64_t n, int32_t m, int32_t* rank, 
     Plan P;
     P.L = make_layout(n, m, 1, 0);
     P.ws = reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(ws), 256));
+    Scal* scal = P.at<Scal>(P.L.scal);
     if (n <= SMALL_PATH_MAX_N && !use_stepwise_peel()) {
         // At most one panel: the sort / tile / persistent-peel pipeline is all launch latency here.
         // Direct n x n test + single-CTA peel: three launches (measured 30 us at n = 200 against 235 us).
         const int words = (int)ceil_div(n, 32);
-        Scal* scal = P.at<Scal>(P.L.scal);
         int rc = small_nds_launch(x, (int)n, m, rank, P.at<uint32_t>(P.L.bits), words, P.at<int>(P.L.count),
                                   &scal->fronts, s);
         if (rc) return rc;
-        int fronts = 0;
-        EVX_CUDA(cudaMemcpyAsync(&fronts, &scal->fronts, sizeof(int), cudaMemcpyDeviceToHost, s));
-        EVX_CUDA(cudaStreamSynchronize(s));
-        g_last_fronts = fronts;
         g_prof.have = false;
-        return EVX_OK;
+        return front_count_post(&scal->fronts, s);
     }
     Prof& pf = g_prof;
     pf.have = false;
@@ -2578,39 +1961,38 @@ extern "C" int evx_nds_f32(const float* x, int64_t n, int32_t m, int32_t* rank, 
     int rc = build(P, x, s, pf.on ? pf.ev[1] : nullptr, pf.on ? pf.ev[2] : nullptr);
     if (rc) return rc;
 
-    // Peel.  The trip count is data dependent (non_dominate.py:78-80): fronts are enqueued in
-    // batches and one flag per front is read back after each batch; steps past the last front are
-    // no-ops (nothing has count 0 any more).
-    Scal* scal = P.at<Scal>(P.L.scal);
-    uint32_t* mask = P.at<uint32_t>(P.L.mask);
-    int host_any[ANY_SLOTS];
-    int k = 0, batch = 8;
-    const bool stepwise = use_stepwise_peel();
+    const bool stepwise = use_stepwise_peel() || !persistent_peel_fits(P.L);
     if (!stepwise) {
-        // default: one persistent cooperative kernel peels every front without host round trips
+        // one persistent cooperative kernel peels every front: no host round trip, nothing blocks
         if ((rc = peel_persistent(P, s))) return rc;
-    }
-    for (; stepwise;) {
-        for (int b = 0; b < batch; ++b) {
-            if ((rc = detect(P, k + b, mask, s))) return rc;
-            if ((rc = apply(P, k + b, mask, &scal->any[b], s))) return rc;
+    } else {
+        // Fallback (EVX_PEEL=stepwise, or a population beyond the persistent kernel's tables): one
+        // detect + apply pair of launches per front.  The trip count is data dependent
+        // (non_dominate.py:78-80), so fronts are enqueued in batches and one flag per front is read back
+        // after each batch - this path blocks the host; steps past the last front are no-ops.
+        uint32_t* mask = P.at<uint32_t>(P.L.mask);
+        int host_any[ANY_SLOTS];
+        int k = 0, batch = 8;
+        for (;;) {
+            for (int b = 0; b < batch; ++b) {
+                if ((rc = detect(P, k + b, mask, s))) return rc;
+                if ((rc = apply(P, k + b, mask, &scal->any[b], s))) return rc;
+            }
+            EVX_CUDA(cudaMemcpyAsync(host_any, scal->any, sizeof(int) * batch, cudaMemcpyDeviceToHost, s));
+            EVX_CUDA(cudaStreamSynchronize(s));
+            int b = 0;
+            while (b < batch && host_any[b]) ++b;
+            if (b < batch) { front_count_set(k + b); break; }
+            k += batch;
+            if (batch < ANY_SLOTS) batch *= 2;
         }
-        EVX_CUDA(cudaMemcpyAsync(host_any, scal->any, sizeof(int) * batch, cudaMemcpyDeviceToHost, s));
-        EVX_CUDA(cudaStreamSynchronize(s));
-        int b = 0;
-        while (b < batch && host_any[b]) ++b;
-        if (b < batch) { g_last_fronts = k + b; break; }
-        k += batch;
-        if (batch < ANY_SLOTS) batch *= 2;
     }
     k_write_ranks<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(P.at<int>(P.L.row2u), P.at<int>(P.L.rank_u), n, 1, 0, rank);
     EVX_LAUNCH_CHECK();
-    if (pf.on) EVX_CUDA(cudaEventRecord(pf.ev[3], s));
-    int fronts_dev = 0;
-    if (!stepwise) EVX_CUDA(cudaMemcpyAsync(&fronts_dev, &scal->fronts, sizeof(int), cudaMemcpyDeviceToHost, s));
-    EVX_CUDA(cudaStreamSynchronize(s));
-    if (!stepwise) g_last_fronts = fronts_dev;
-    if (pf.on) {
+    if (!stepwise && (rc = front_count_post(&scal->fronts, s))) return rc;
+    if (pf.on) {                                                    // profiling mode only: blocks to read the events
+        EVX_CUDA(cudaEventRecord(pf.ev[3], s));
+        EVX_CUDA(cudaEventSynchronize(pf.ev[3]));
         EVX_CUDA(cudaEventElapsedTime(&pf.prep_ms, pf.ev[0], pf.ev[1]));
         EVX_CUDA(cudaEventElapsedTime(&pf.tiles_ms, pf.ev[1], pf.ev[2]));
         EVX_CUDA(cudaEventElapsedTime(&pf.peel_ms, pf.ev[2], pf.ev[3]));
@@ -2632,7 +2014,7 @@ extern "C" int evx_profile_last(float* prep_ms, float* tiles_ms, float* peel_ms)
 
 extern "C" int evx_nds_host_f32(const float* x_host, int64_t n, int32_t m, int32_t* rank_host) {
     EVX_REQUIRE(n >= 0 && m >= 1 && m <= EVX_MAX_OBJECTIVES, EVX_ERR_ARG, "evx_nds_host_f32: bad shape");
-    if (n == 0) { g_last_fronts = 0; return EVX_OK; }
+    if (n == 0) { front_count_set(0); return EVX_OK; }
     EVX_REQUIRE(x_host && rank_host, EVX_ERR_ARG, "evx_nds_host_f32: null pointer");
     const size_t wsb = evx_nds_workspace_bytes(n, m);
     EVX_REQUIRE(wsb != 0, EVX_ERR_ARG, "evx_nds_host_f32: n too large");

@@ -107,7 +107,8 @@ class FusedShardedNonDominatedSort:
     """Same result as ShardedNonDominatedSort, but the whole peel is ONE persistent kernel per rank:
     front members travel between GPUs as peer stores over NVLink inside the kernel, and the per-front
     barrier spans all ranks' CTAs - no NCCL call and no kernel launch per front.  Needs peer-mapped
-    memory, obtained from torch symmetric memory (plumbing only)."""
+    memory, obtained from torch symmetric memory (plumbing only).  The peer state is cleared once, here;
+    calls need no host-level hand-shake between them and never block the host."""
 
     def __init__(self, n, m, group=None):
         import ctypes
@@ -125,21 +126,27 @@ class FusedShardedNonDominatedSort:
         self.handle = symm.rendezvous(self.peer, self.group.group_name)
         ptrs = list(self.handle.buffer_ptrs)
         self._ptrs = (ctypes.c_void_p * self.world)(*ptrs)
-        self._nf = ctypes.c_int32(0)
         self.out = torch.zeros(n, dtype=torch.int32, device=self.shard.device)
-        self.num_fronts = 0
+        self._reset()
+
+    def _reset(self):
+        """Clear this rank's peer state and wait until every rank has done so (once per plan, and again
+        only after a time-out)."""
+        check(lib().evx_nds_shard_peer_init(self.shard.plan, self.peer.data_ptr(), stream_ptr()))
+        torch.cuda.current_stream().synchronize()
+        dist.barrier(group=self.group)
+
+    @property
+    def num_fronts(self):
+        """Fronts found by the last call (waits for that call's kernels)."""
+        return int(lib().evx_nds_last_num_fronts())
 
     def __call__(self, x):
-        import ctypes
         if self.n == 0:
             return self.out
         L = lib()
         self.shard.build(x)
-        check(L.evx_nds_shard_peer_init(self.shard.plan, self.peer.data_ptr(), stream_ptr()))
-        torch.cuda.current_stream().synchronize()
-        dist.barrier(group=self.group)                 # every rank's peer state is clean before anyone writes to it
-        check(L.evx_nds_shard_peel_fused(self.shard.plan, self._ptrs, ctypes.byref(self._nf), stream_ptr()))
-        self.num_fronts = int(self._nf.value)
+        check(L.evx_nds_shard_peel_fused(self.shard.plan, self._ptrs, None, stream_ptr()))
         self.shard.ranks(self.out)
         dist.all_reduce(self.out, op=dist.ReduceOp.SUM, group=self.group)
         return self.out

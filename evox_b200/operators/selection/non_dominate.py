@@ -90,37 +90,51 @@ def crowding_distance_sort(x, mask=None):
     return out
 
 
-def _lexsort2(secondary, primary):
-    """np.lexsort((secondary, primary)): stable sort by primary, ties by secondary."""
-    o = torch.sort(secondary, stable=True).indices
-    return o[torch.sort(primary[o], stable=True).indices]
-
-
 def non_dominate(population, fitness, topk, deduplicate):
-    """Survivor selection.  non_dominate.py:183-222; the host glue (argsort / lexsort / gather) is
-    torch here where it is jnp in the reference, and keeps the reference's :216/:218 key choice: the
-    secondary key is the negated crowding *argsort permutation*."""
+    """Survivor selection.  non_dominate.py:183-222.  Everything after the optional de-duplication
+    (:210-222: non-dominated sort, cut rank, crowding permutation of the cut front, the final lexsort
+    and the gather) is ONE library call, evx_non_dominate_f32, which keeps the reference's :216/:218
+    key choice: the secondary key is the negated crowding *argsort permutation*.  The de-duplication
+    (:188-208, `jnp.unique(axis=0, size=n)` with its index padding) stays host glue, as SURVEY 8 f1 says."""
     pop = population if isinstance(population, torch.Tensor) else torch.as_tensor(population)
     pop = pop.to("cuda")
     fit = as_f32_cuda(fitness, "fitness")
-    fit_bak = fit
+    n = pop.shape[0]
+    if fit.dim() != 2 or fit.shape[0] != n:
+        raise ValueError(f"non_dominate: population {tuple(pop.shape)} and fitness {tuple(fit.shape)} disagree")
+    topk = int(topk)
+    if not 1 <= topk <= n:
+        raise ValueError(f"non_dominate: topk={topk} must be in [1, {n}]")
+    fit_bak = None
     if deduplicate:
-        n = pop.shape[0]
         uniq, inverse = torch.unique(pop, dim=0, return_inverse=True)
         count = uniq.shape[0]
         ar = torch.arange(n, device="cuda")
         first = torch.full((count,), n, dtype=torch.long, device="cuda").scatter_reduce(0, inverse, ar, "amin")
         uidx = torch.cat([first, first[:1].expand(n - count)])          # jnp.unique(size=n) index padding
         pop, fit = pop[uidx], fit[uidx]
-        fit_bak = fit
-        fit = torch.where((ar < count)[:, None], fit, torch.full_like(fit, float("inf")))
-    rank = non_dominated_sort(fit)
-    order = torch.sort(rank, stable=True).indices
-    worst = rank[order[topk - 1]]
-    mask = rank == worst
-    cd_perm = crowding_distance_sort(fit, mask)
-    combined = _lexsort2(-cd_perm, rank)[:topk]
-    return pop[combined], fit_bak[combined]
+        fit_bak = fit.contiguous()
+        fit = torch.where((ar < count)[:, None], fit, torch.full_like(fit, float("inf"))).contiguous()
+    m = fit.shape[1]
+    pop2 = pop.reshape(n, -1)
+    fused_pop = pop2.dtype == torch.float32 and pop2.shape[1] > 0
+    pop2 = pop2.contiguous() if fused_pop else pop2
+    d = pop2.shape[1] if fused_pop else 0
+    out_fit = torch.empty((topk, m), dtype=torch.float32, device="cuda")
+    out_pop = torch.empty((topk, d), dtype=torch.float32, device="cuda") if fused_pop else None
+    out_idx = None if fused_pop else torch.empty((topk,), dtype=torch.int32, device="cuda")
+    L = lib()
+    nbytes = L.evx_non_dominate_workspace_bytes(n, m)
+    if nbytes == 0:
+        raise ValueError(f"non_dominate: unsupported shape n={n}, m={m}")
+    ws = workspace(nbytes, "sel")
+    check(L.evx_non_dominate_f32(pop2.data_ptr() if fused_pop else None, fit.data_ptr(),
+                                 None if fit_bak is None else fit_bak.data_ptr(), n, d, m, topk,
+                                 None if out_pop is None else out_pop.data_ptr(), out_fit.data_ptr(),
+                                 None if out_idx is None else out_idx.data_ptr(), ws.data_ptr(), ws.numel(), stream_ptr()))
+    if fused_pop:
+        return out_pop.reshape((topk,) + tuple(pop.shape[1:])), out_fit
+    return pop[out_idx.long()], out_fit                                  # non-float32 populations: gather by index
 
 
 class NonDominate:

@@ -51,13 +51,17 @@ int evx_dominate_relation_bits(const float* x, int64_t nx, const float* y, int64
  * replaces operators/selection/non_dominate.py:32-115  `non_dominated_sort(x, method)`
  * (all three `method`s compute the same ranks; this is the one implementation behind them).
  * x: device float32 [n, m];  rank: device int32 [n], front index starting at 0, bit-exact.
- * Synchronises (the number of fronts is data dependent, non_dominate.py:78-80).                    */
+ * Asynchronous: the data-dependent front loop (non_dominate.py:78-80) runs inside one persistent kernel,
+ * the host never waits.  (Two documented exceptions block the host: n > 2M rows, and EVX_PEEL=stepwise in
+ * the environment - both take a one-front-per-launch path that reads one flag per front back.)         */
 size_t evx_nds_workspace_bytes(int64_t n, int32_t m);
 int evx_nds_f32(const float* x, int64_t n, int32_t m, int32_t* rank, void* ws, size_t ws_bytes,
                 void* stream);
 /* Same, host buffers in and out (H2D + D2H inside; library arena for scratch).                    */
 int evx_nds_host_f32(const float* x_host, int64_t n, int32_t m, int32_t* rank_host);
-/* Number of fronts found by the last evx_nds_* call on this host thread.                          */
+/* Number of fronts found by the last evx_nds_* / evx_non_dominate_f32 call on this host thread.  The call
+ * leaves a copy of the device-side count in flight; this function waits for it (it is the only place
+ * that blocks).  -1: not available (call made during a stream capture, or a peer timed out).        */
 int32_t evx_nds_last_num_fronts(void);
 
 /* ---- non-dominated sort without any device allocation -------------------------------------------
@@ -98,6 +102,22 @@ int evx_crowding_distance_f32(const float* costs, const uint8_t* mask, int64_t n
                               float* dist, void* ws, size_t ws_bytes, void* stream);
 int evx_crowding_distance_sort_f32(const float* costs, const uint8_t* mask, int64_t n, int32_t m,
                                    int32_t* order, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- (f1) survivor selection --------------------------------------------------------------------
+ * replaces operators/selection/non_dominate.py:210-222, the body of `non_dominate(population, fitness,
+ * topk, deduplicate)` after its optional de-duplication (:188-208 stays with the caller): non-dominated
+ * sort, cut rank, crowding-distance permutation of the cut front, lexsort((-permutation, rank))[:topk]
+ * - including the reference's choice of the argsort PERMUTATION as tie-breaker (:216/:218) - and the
+ * gather of the chosen rows, in the reference's output order.
+ * pop: device float32 [n, d] (may be NULL with out_pop NULL); fit: device float32 [n, m], what is ranked;
+ * fit_out_src: device float32 [n, m] gathered into out_fit (NULL = fit; the de-duplicating caller passes
+ * the fitness backup of :201); 1 <= topk <= n.  Outputs (each may be NULL): out_pop [topk, d],
+ * out_fit [topk, m], out_index int32 [topk] (row numbers chosen, for populations that are not float32).
+ * Asynchronous on `stream`.                                                                          */
+size_t evx_non_dominate_workspace_bytes(int64_t n, int32_t m);
+int evx_non_dominate_f32(const float* pop, const float* fit, const float* fit_out_src, int64_t n, int32_t d,
+                         int32_t m, int64_t topk, float* out_pop, float* out_fit, int32_t* out_index,
+                         void* ws, size_t ws_bytes, void* stream);
 
 /* ---- (a7) DTLZ1..7 evaluate -------------------------------------------------------------------
  * replaces problems/numerical/dtlz.py:48-69, 84-103, 115-145, 152-172, 188-208, 244-265, 303-322
@@ -147,12 +167,18 @@ int evx_nds_shard_detect(evx_nds_shard* p, int32_t k, uint32_t* local_mask, void
 int evx_nds_shard_apply(evx_nds_shard* p, int32_t k, const uint32_t* all_masks, int32_t* any_out,
                         void* stream);
 /* Fused alternative to the detect / all-gather / apply loop: ONE persistent kernel per rank peels
- * every front; new front members are written straight into every rank's list over NVLink (peer
- * stores + system-scope atomics) and a barrier over all CTAs of all ranks separates the fronts.
- * Each rank provides `peer_bytes` of peer-mapped memory (e.g. torch symmetric memory);
+ * every front.  Every rank holds a replica of the current front (per-panel member lists) in peer-mapped
+ * memory; the warp that finds a panel's new members stores them straight into every rank's replica over
+ * NVLink (plain peer stores, no cross-GPU atomics), and a barrier over all CTAs of all ranks separates
+ * the fronts: local arrival counter, one 64-bit message per rank pair, every CTA polls its own GPU's
+ * message words.  Each rank provides `peer_bytes` of peer-mapped memory (e.g. torch symmetric memory);
  * peer_bufs[r] (HOST array of world device pointers) is rank r's buffer as mapped in this process.
- * Sequence: build -> peer_init -> host-level barrier across ranks -> peel_fused (synchronises; fails
- * with a message, never hangs, if a rank is more than 4 s late) -> ranks.  world <= 8.              */
+ * Sequence: peer_init ONCE per plan -> host-level barrier across ranks -> then, per population,
+ * build -> peel_fused -> ranks, with no further hand-shake between calls (barrier epochs continue
+ * across launches and every launch ends with a barrier).  num_fronts == NULL: asynchronous, the front
+ * count is available from evx_nds_last_num_fronts(); otherwise the call waits and fails with a message
+ * (never hangs) if a rank was more than 4 s late - after which peer_init + host barrier are needed
+ * again.  world <= 8, n <= 2M.                                                                       */
 size_t evx_nds_shard_peer_bytes(const evx_nds_shard* p);
 int evx_nds_shard_peer_init(evx_nds_shard* p, void* local_peer_buf, void* stream);
 int evx_nds_shard_peel_fused(evx_nds_shard* p, void* const* peer_bufs, int32_t* num_fronts, void* stream);
@@ -169,9 +195,9 @@ void evx_launch_count_reset(void);
 void evx_profile_enable(int32_t on);
 int evx_profile_last(float* prep_ms, float* tiles_ms, float* peel_ms);
 /* nanoseconds the persistent peel kernel of the plan's last run spent in {accumulate, merge+commit,
- * barrier, fronts} as seen by its first CTA (out16[0..3]) and its last CTA (out16[4..7]); out16[8..14]:
- * steps of the multi-rank barrier as seen by CTA 0 (own fence+arrive, local wait, fence, send, peer
- * wait, fence, release), summed over fronts.  p == NULL: the values of this host thread's last
+ * barrier, fronts} as seen by its first CTA (out16[0..3]) and its last CTA (out16[4..7]); out16[8..10]:
+ * steps of the multi-rank barrier as seen by CTA 0 (fence + arrive, waiting for every rank's message,
+ * acquire fence), summed over fronts.  p == NULL: the values of this host thread's last
  * evx_nds_f32 call made with evx_profile_enable(1).                                                 */
 int evx_debug_peel_times(evx_nds_shard* p, uint64_t* out16);
 /* register-only issue-rate probe: runs `iters` dependent-free compare+logic steps per thread on
