@@ -22,23 +22,21 @@
 //      bytes.  A pair and the dominator counts of its columns are owned by one rank (P mod world).
 //   7. Peeling: front k = columns whose count is 0.  Every front row is read exactly once per pair,
 //      rows are summed bit-sliced (carry-save adders), subtracted from bit-sliced counts, and
-//      "count == 0" is the NOR of the planes.  One persistent cooperative kernel peels all fronts:
-//      k_peel_dynamic re-balances the work over the CTAs for every front (one GPU); on several GPUs
-//      k_peel_persistent<true> (fixed ownership) also exchanges front membership over NVLink peer
-//      memory inside the kernel.
+//      "count == 0" is the NOR of the planes.  One persistent cooperative kernel (k_peel_dynamic) peels
+//      all fronts and re-balances the work over the CTAs for every front; on several GPUs the same
+//      kernel also exchanges front membership over NVLink peer memory.  Fronts are separated by data
+//      dependence on epoch-tagged words, not by a barrier.
 //
 // File map: geometry and workspace layout - sort / unique / labels - tile kernels (word_fail, f2_mask,
 // slab_out, counts_flush, tile_offdiag, tile_diag) - one-front-per-launch peel (k_front_detect /
-// k_mask_to_list / k_front_apply) - fixed-ownership persistent peel with the multi-rank exchange
-// (world_barrier, k_peel_persistent) - load-balanced persistent peel (world_barrier_seg,
+// k_mask_to_list / k_front_apply) -
+// tagged front words and the persistent load-balanced peel (front_row, peel_commit_seg, publish_pending,
 // k_peel_dynamic) - host side (launch_tiles, build, detect / apply, peel_persistent) - C entry points.
-#include <cooperative_groups.h>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
 #include <cstdlib>
 #include <cstring>
-#include <vector>
 
 #include <type_traits>
 
@@ -66,9 +64,8 @@ struct Scal {
     int nf[2];      // one-front-per-launch peel: size of the current front list, double buffered by front parity
     int any[ANY_SLOTS];
     int fronts;     // persistent peel: number of fronts found (-1: a peer timed out)
-    unsigned int barrier;   // persistent peel: grid barrier arrivals (monotonic within a launch)
+    unsigned int arrived;   // persistent peel, one GPU: panels published so far in this launch (see PeerState::arrived)
     unsigned long long dbg[8];   // persistent peel: ns spent by CTA 0 / last CTA in accumulate, merge+commit, barrier
-    unsigned long long bdbg[8];  // world barrier, CTA 0: ns in {fence + arrive, waiting for the messages, acquire fence}
 };
 
 struct Layout {
@@ -140,14 +137,14 @@ static Layout make_layout(int64_t n, int m, int world, int rank) {
     L.row2u = take(sizeof(int) * n);
     L.count = take(sizeof(int) * (size_t)L.npl_max * TW);
     L.rank_u = take(sizeof(int) * (size_t)L.npl_max * TW);
-    L.flist = take(sizeof(int) * L.npad);
-    L.flist2 = take(sizeof(int) * L.npad);
+    L.flist = take(sizeof(uint64_t) * L.npad);                   // front segments (64-bit tagged words), double buffered;
+    L.flist2 = take(sizeof(uint64_t) * L.npad);                  // the one-front-per-launch peel uses the first as an int list
     L.kplanes = 1;
     while ((1ll << L.kplanes) <= L.npad) ++L.kplanes;          // counts < npad fit in kplanes bits
     L.cplanes = take(sizeof(uint32_t) * (size_t)L.npl_max * (L.kplanes + 1) * PW);
     L.mask = take(sizeof(uint32_t) * (size_t)L.npl_max * PW * world);
     L.partials = take(sizeof(uint32_t) * (size_t)(PEEL_MAX_GRID + L.npl_max / 2 + 1) * PEEL_KMAX * 64);
-    L.pcnt = take(sizeof(int) * 3 * (size_t)(L.npl_max + 2));          // per-panel front sizes, triple buffered
+    L.pcnt = take(sizeof(uint64_t) * 2 * (size_t)(L.np + 2));          // per-panel front sizes (tagged words), double buffered
     L.pdone = take(sizeof(unsigned int) * 2 * (size_t)L.npl_max);      // arrivals, commits
     L.scal = take(sizeof(Scal));
     L.bits_words = pair_words_before(L.npl / 2, world, rank);
@@ -846,22 +843,29 @@ struct Planes {
 
 // ---- peer-visible state of the fused multi-rank peel ------------------------------------------------
 // Every rank provides one buffer in peer-mapped memory (torch symmetric memory / CUDA IPC):
-// [PeerState | per-panel front sizes x 3 | front segments A | front segments B], a full replica of the
-// front (all panels of all ranks).  The warp that commits a panel writes the panel's new members and
-// their number straight into EVERY rank's replica (posted stores over NVLink, no cross-GPU atomics).
-// The per-front barrier: every CTA fences its pushes at system scope and arrives on a LOCAL counter;
-// the last local arriver sends one 64-bit message (the epoch) to every rank; every CTA of every rank
-// polls its own rank's message words.  Messages are double buffered by epoch parity: a rank can be at
-// most one barrier ahead of a peer that has not read its previous message yet.  Epochs run on across
-// launches (PeerState::epoch_base) and every launch ends with one more barrier, after which no CTA of
-// any rank still reads the replica - so the next launch needs neither a reset of this state nor a
-// host-level hand-shake: the buffer is cleared once, by evx_nds_shard_peer_init.
+// [PeerState | per-panel front sizes x 2 | front segments A | front segments B], a full replica of the
+// front (all panels of all ranks), made of 64-bit words (value, epoch).  The warp that commits a panel
+// writes the panel's new members straight into EVERY rank's replica, and the CTA publishes the sizes of
+// the panels it committed when it is done with the front (plain 8-byte stores, posted over NVLink: no
+// cross-GPU atomics on data, no system-scope fence).  There is NO barrier between fronts, on one GPU or
+// on eight: a CTA starts front f when all panels' size words carry f's epoch, and reads a member word
+// only once it carries it too.  Reuse of the double buffers is safe by data dependence: a rank writes
+// front f+2 only after it has seen every rank's sizes of front f+1, and a rank publishes its last size
+// of front f+1 only after its last read of front f.
+// So that waiting CTAs do not hammer the size words, every CTA adds the number of panels it published
+// to a counter on every rank (one relaxed reduction per rank); one thread per CTA polls its own GPU's
+// counter and the CTA looks at the size words when the counter says they should all be there.  The
+// counter is a hint only: validity is decided by the words themselves.
+// Epochs and the counter run on across launches (PeerState::epoch_base / arrived_base; every rank
+// passes the same number of fronts), so stale words never validate and the next launch needs neither a
+// reset nor a host-level hand-shake: the buffer is cleared once, by evx_nds_shard_peer_init.
 constexpr int MAX_WORLD = 8;
 struct PeerState {
-    unsigned long long xmsg[2][MAX_WORLD];  // [epoch & 1][source rank] = epoch of that rank's last arrival
-    int abort;
-    unsigned int epoch_base;                // barriers this rank has passed in all earlier launches (local use only)
-    unsigned int pad[30];
+    int abort;                              // a rank gave up waiting (4 s): everybody leaves
+    unsigned int epoch_base;                // epoch of the last front of the previous launch (local use only)
+    unsigned int arrived;                   // panels published to this replica so far, all launches (a hint)
+    unsigned int arrived_base;              // its value when the previous launch was complete (local use only)
+    unsigned int pad[60];
 };
 static_assert(sizeof(PeerState) == 256, "PeerState must stay 256 bytes");
 struct PeerTable {
@@ -919,30 +923,26 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)_
 // adds them up and commits - nobody waits.  Count planes live in global memory (L2).
 // ------------------------------------------------------------------------------------------------
 
-__device__ __forceinline__ void grid_barrier_plain(unsigned int* ctr, unsigned int& epoch) {
-    __syncthreads();
-    ++epoch;
-    if (threadIdx.x == 0) {
-        // release-add (publishes what the CTA wrote before the __syncthreads), relaxed polling, one acquire fence
-        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
-        const unsigned int target = epoch * gridDim.x;
-        unsigned int v;
-        do {
-            asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
-        } while (v < target);
-        asm volatile("fence.acq_rel.gpu;" ::: "memory");
-    }
-    __syncthreads();
+// Front data words are 64 bits: low half = value, high half = the epoch it was written for.  A word is
+// valid for front epoch e iff its high half equals e, so a reader needs no fence and no barrier with a
+// writer on another GPU (8-byte stores arrive whole): it polls the word itself.
+typedef unsigned long long FWord;
+__device__ __forceinline__ FWord fword(int value, unsigned int epoch) {
+    return ((FWord)epoch << 32) | (unsigned int)value;
 }
 
 // Position t of the virtual front list restricted to panels [0, npre): the member's row index.
-__device__ __forceinline__ int front_row(const int* pre, int npre, const int* seg, int t) {
+__device__ __forceinline__ int front_row(const int* pre, int npre, const FWord* seg, int t, unsigned int fe) {
     int lo = 0, hi = npre;                            // pre[lo] <= t < pre[hi]
     while (hi - lo > 1) {
         const int mid = (lo + hi) >> 1;
         if (pre[mid] <= t) lo = mid; else hi = mid;
     }
-    return __ldcg(seg + (size_t)lo * TW + (t - pre[lo]));
+    const FWord* w = seg + (size_t)lo * TW + (t - pre[lo]);
+    FWord v = __ldcg(w);
+    while ((unsigned int)(v >> 32) != fe)             // a peer's size word overtook its members on the way: rare
+        asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(w) : "memory");
+    return (int)(unsigned int)v;
 }
 
 // ---- cp.async gather ring (load-balanced kernel) ----------------------------------------------------
@@ -990,15 +990,15 @@ __device__ __forceinline__ void ring2_drain(Ring2& rg, int lane, Planes& pa, Pla
 
 // Groups g0 + first, g0 + first + stride, ... < g1 of pair Q's list prefix.
 // (first, stride) = (warp, PEEL_WARPS) when the CTA shares the groups, (0, 1) when one warp does them all.
-__device__ __forceinline__ void peel_accumulate_groups(const int* pre, int npre, int rows, const int* seg, int g0, int g1,
-                                                       int first, int stride, int lane, const uint32_t* pair, Ring2& rg,
-                                                       Planes& pa, Planes& pb) {
+__device__ __forceinline__ void peel_accumulate_groups(const int* pre, int npre, int rows, const FWord* seg, unsigned int fe,
+                                                       int g0, int g1, int first, int stride, int lane,
+                                                       const uint32_t* pair, Ring2& rg, Planes& pa, Planes& pb) {
     const int sub = lane >> 4, part = (lane & 15) * 4;              // which of the two rows / which 16 bytes of it
     int g = g0 + first;
-    int mine = (g < g1 && g * 32 + lane < rows) ? front_row(pre, npre, seg, g * 32 + lane) : -1;
+    int mine = (g < g1 && g * 32 + lane < rows) ? front_row(pre, npre, seg, g * 32 + lane, fe) : -1;
     for (; g < g1; g += stride) {
         const int gn = g + stride;
-        const int nxt = (gn < g1 && gn * 32 + lane < rows) ? front_row(pre, npre, seg, gn * 32 + lane) : -1;
+        const int nxt = (gn < g1 && gn * 32 + lane < rows) ? front_row(pre, npre, seg, gn * 32 + lane, fe) : -1;
         const uint32_t valid = __ballot_sync(0xFFFFFFFFu, mine >= 0);     // a prefix of the lanes
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
@@ -1029,14 +1029,39 @@ __device__ __forceinline__ void peel_accumulate_groups(const int* pre, int npre,
     }
 }
 
+// What a CTA has committed for the coming front but not yet published: the panels' size words go out
+// together when the CTA is done with the front (publish_pending), behind ONE fence, instead of one fence
+// per panel.
+constexpr int PUB_CAP = 64;
+struct PubList {
+    int n;                  // panels committed so far for the coming front (may exceed PUB_CAP)
+    int extra;              // panels already published directly (list full, or untouched panels)
+    int J[PUB_CAP], cnt[PUB_CAP];
+};
+
+// Store one size word into the local replica and, fused multi-rank, into every peer's.
+template <bool MULTI>
+__device__ __forceinline__ void store_count(FWord* cnt_next_J, int cnt, unsigned int fe_next, const PeerTable& pt) {
+    const FWord w = fword(cnt, fe_next);
+    __stcg(cnt_next_J, w);
+    if constexpr (MULTI) {
+        if (pt.world > 1) {
+            const size_t coff = reinterpret_cast<const char*>(cnt_next_J) - pt.base[pt.rank];
+            for (int r = 0; r < pt.world; ++r)
+                if (r != pt.rank) *reinterpret_cast<volatile FWord*>(pt.base[r] + coff) = w;
+        }
+    }
+}
+
 // One warp: subtract a bit-sliced delta (plane p of this lane's word = delta(p), p < pm; pm = 0: none)
 // from panel J's count planes in global memory, retire the columns that reached zero, write their
-// rank and append them, in column order, as panel J's segment of the next front.  MULTI: the segment
-// and its size go into every rank's replica of the front (plain stores to peer-mapped memory, posted
-// over NVLink; the barrier that follows fences them).
+// rank and append them, in column order, as panel J's segment of the next front (epoch fe_next).
+// MULTI: the segment goes into every rank's replica of the front (plain 8-byte stores to peer-mapped
+// memory, posted over NVLink).  The segment's size is queued in `pub`.
 template <bool MULTI, class Delta>
-__device__ __forceinline__ void peel_commit_seg(uint32_t* cp, int K, Delta delta, int pm, int lane, int J, int* seg_next,
-                                                int* cnt_next, int* rank_panel, int rank_value, const PeerTable& pt) {
+__device__ __forceinline__ void peel_commit_seg(uint32_t* cp, int K, Delta delta, int pm, int lane, int J, FWord* seg_next,
+                                                FWord* cnt_next, unsigned int fe_next, int* rank_panel, int rank_value,
+                                                const PeerTable& pt, PubList* pub) {
     uint32_t c[PEEL_KMAX];
 #pragma unroll
     for (int p = 0; p < PEEL_KMAX; ++p) c[p] = (p < K) ? __ldcg(cp + p * PW + lane) : 0u;   // all planes in flight at once
@@ -1062,38 +1087,62 @@ __device__ __forceinline__ void peel_commit_seg(uint32_t* cp, int K, Delta delta
         const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
         if (lane >= o) incl += t;
     }
-    int* dst = seg_next + (size_t)J * TW + (incl - cnt);
-    if (lane == 31 && incl) __stcg(cnt_next, incl);          // (the slot was cleared two fronts ago)
+    FWord* dst = seg_next + (size_t)J * TW + (incl - cnt);
     uint32_t w = nw;
     const int c0 = lane * 32;
-    if constexpr (MULTI) {
-        if (pt.world > 1) {
-            const char* mine = pt.base[pt.rank];
-            const size_t coff = reinterpret_cast<const char*>(cnt_next) - mine;
-            const size_t soff = reinterpret_cast<const char*>(dst) - mine;
-            if (lane == 31 && incl) {
-                for (int r = 0; r < pt.world; ++r)
-                    if (r != pt.rank) *reinterpret_cast<volatile int*>(pt.base[r] + coff) = incl;
-            }
-            int q = 0;
-            while (w) {
-                const int b = __ffs(w) - 1;
-                w &= w - 1;
-                const int v = J * TW + c0 + b;
-                __stcg(dst + q, v);
-                for (int r = 0; r < pt.world; ++r)
-                    if (r != pt.rank) reinterpret_cast<volatile int*>(pt.base[r] + soff)[q] = v;
-                rank_panel[c0 + b] = rank_value;
-                ++q;
-            }
-            return;
-        }
-    }
+    int q = 0;
     while (w) {
         const int b = __ffs(w) - 1;
         w &= w - 1;
-        __stcg(dst++, J * TW + c0 + b);
+        const FWord v = fword(J * TW + c0 + b, fe_next);
+        __stcg(dst + q, v);
+        if constexpr (MULTI) {
+            if (pt.world > 1) {
+                const size_t soff = reinterpret_cast<const char*>(dst + q) - pt.base[pt.rank];
+                for (int r = 0; r < pt.world; ++r)
+                    if (r != pt.rank) *reinterpret_cast<volatile FWord*>(pt.base[r] + soff) = v;
+            }
+        }
         rank_panel[c0 + b] = rank_value;
+        ++q;
+    }
+    __syncwarp();
+    if (lane == 31) {
+        const int slot = atomicAdd(&pub->n, 1);
+        if (slot < PUB_CAP) {
+            pub->J[slot] = J;
+            pub->cnt[slot] = incl;
+        } else {                                      // list full: publish now, behind a fence of its own
+            __threadfence();
+            store_count<MULTI>(cnt_next + J, incl, fe_next, pt);
+        }
+    }
+}
+
+// End of a CTA's work on a front: publish the size words of the panels it committed (after one fence
+// that covers every warp's planes, ranks and members), then tell every rank how many panels this CTA
+// has published for the coming front.
+template <bool MULTI>
+__device__ __forceinline__ void publish_pending(PubList* pub, FWord* cnt_next, unsigned int fe_next, Scal* scal,
+                                                const PeerTable& pt) {
+    __syncthreads();                                  // every warp's commits are issued
+    if (threadIdx.x == 0) {
+        const int n = pub->n, listed = n < PUB_CAP ? n : PUB_CAP;
+        const unsigned int total = (unsigned int)(n + pub->extra);
+        __threadfence();                              // cumulative over the CTA barrier: planes, ranks, members
+        for (int i = 0; i < listed; ++i) store_count<MULTI>(cnt_next + pub->J[i], pub->cnt[i], fe_next, pt);
+        pub->n = 0;                                   // (the next commits are several CTA barriers away)
+        pub->extra = 0;
+        if (total) {
+            if constexpr (MULTI) {
+                asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(&peer_state(pt, pt.rank)->arrived), "r"(total) : "memory");
+                for (int r = 0; r < pt.world; ++r)
+                    if (r != pt.rank)
+                        asm volatile("red.relaxed.sys.global.add.u32 [%0], %1;" ::"l"(&peer_state(pt, r)->arrived), "r"(total) : "memory");
+            } else {
+                asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(&scal->arrived), "r"(total) : "memory");
+            }
+        }
     }
 }
 
@@ -1125,75 +1174,13 @@ __device__ __forceinline__ int pair_fixed_cost(int total) {      // total = grou
     return total <= PEEL_WARP_PAIR_GROUPS + PEEL_COST_WARP_PAIR ? PEEL_COST_WARP_PAIR : PEEL_COST_CTA_PAIR;
 }
 
-// Barrier over all CTAs of all ranks.  The front exchange itself is already under way when a CTA gets
-// here: committers wrote their panels' new members into every rank's replica.  Each CTA makes its own
-// pushes visible system-wide (one thread fences after the CTA barrier: the fence is cumulative over
-// it), then arrives on the local counter; whoever arrives last on this GPU sends the epoch to every
-// rank.  Every CTA polls the `world` message words of its own rank - nobody relays a release.  Critical
-// path: slowest CTA's fence + arrive -> one NVLink store -> poll -> acquire fence.
-// Returns 0, or -1 after a time-out or a protocol error (every CTA of every rank then leaves).
-// dbg (CTA 0, thread 0): bdbg[0] += fence + arrive, bdbg[1] += waiting for the messages, bdbg[2] += acquire fence.
-__device__ __forceinline__ int world_barrier_seg(Scal* scal, unsigned int& epoch, unsigned int ebase, const PeerTable& pt,
-                                                 int* flag_smem) {
-    __syncthreads();
-    ++epoch;
-    const unsigned int gepoch = ebase + epoch;                                   // epoch across launches
-    const unsigned long long t0 = global_ns();
-    if (threadIdx.x == 0) {
-        *flag_smem = 0;
-        if (pt.world > 1) asm volatile("fence.acq_rel.sys;" ::: "memory");       // this CTA's pushes are performed
-        unsigned int old;
-        asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(old) : "l"(&scal->barrier) : "memory");
-        if (old + 1u == epoch * gridDim.x) {                                     // last CTA of this GPU to arrive
-            asm volatile("fence.acq_rel.sys;" ::: "memory");                      // ... cumulative over the others' releases
-            const unsigned long long msg = (unsigned long long)gepoch << 32;
-            for (int r = 0; r < pt.world; ++r)
-                asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(&peer_state(pt, r)->xmsg[gepoch & 1u][pt.rank]),
-                             "l"(msg)
-                             : "memory");
-        }
-        if (blockIdx.x == 0) scal->bdbg[0] += global_ns() - t0;
-    }
-    __syncthreads();
-    if (threadIdx.x < pt.world) {
-        PeerState* me = peer_state(pt, pt.rank);
-        const unsigned long long* word = &me->xmsg[gepoch & 1u][threadIdx.x];
-        bool dead = false;
-        unsigned int spins = 0;
-        for (;;) {
-            unsigned long long m;
-            asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(m) : "l"(word) : "memory");
-            const unsigned int e = (unsigned int)(m >> 32);
-            if (e == gepoch) break;
-            if ((int)(e - gepoch) > 0) { dead = true; break; }                   // a peer is two barriers ahead: protocol error
-            if ((++spins & 63u) == 0u) {
-                int ab;
-                asm volatile("ld.relaxed.sys.global.s32 %0, [%1];" : "=r"(ab) : "l"(&me->abort) : "memory");
-                if (ab || global_ns() - t0 > PEER_TIMEOUT_NS) { dead = true; break; }
-            }
-        }
-        if (dead) {
-            for (int r = 0; r < pt.world; ++r)
-                asm volatile("st.relaxed.sys.global.s32 [%0], %1;" ::"l"(&peer_state(pt, r)->abort), "r"(1) : "memory");
-            *flag_smem = -1;
-        }
-        const unsigned long long t1 = global_ns();
-        asm volatile("fence.acq_rel.sys;" ::: "memory");                          // acquire: the peers' pushes are visible
-        if (blockIdx.x == 0 && threadIdx.x == 0) {
-            scal->bdbg[1] += t1 - t0;
-            scal->bdbg[2] += global_ns() - t1;
-        }
-    }
-    __syncthreads();
-    return *flag_smem;
-}
-
 struct DynShared {
     alignas(128) uint32_t merge[PEEL_WARPS][PEEL_PM][PW2];    // per-warp count planes of the pair being merged
     alignas(128) uint32_t acc[PEEL_KMAX][PW2];                // this CTA's sums for the pair (all passes)
     alignas(128) uint32_t ring[PEEL_WARPS][DYN_STAGES * DYN_STAGE_ROWS][PW2];   // per-warp cp.async gather ring
-    int nf;
+    int nf, dead;
     int cnt[8], cnt2[8];
+    PubList pub;
 };
 
 // A warp's register planes -> its shared-memory region, planes [0, pm).  Lane l: word l of panel 0 (pa) and of panel 1 (pb).
@@ -1209,8 +1196,8 @@ __device__ __forceinline__ void store_planes(uint32_t (*m)[PW2], const Planes& p
 
 template <bool MULTI>
 __global__ void __launch_bounds__(PEEL_WARPS * 32, 2)
-k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count, int* __restrict__ rank_u, int* segA,
-               int* segB, Scal* scal, uint32_t* __restrict__ cplanes, int* pcnt, int pstride, uint32_t* partials,
+k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count, int* __restrict__ rank_u, FWord* segA,
+               FWord* segB, Scal* scal, uint32_t* __restrict__ cplanes, FWord* pcnt, int pstride, uint32_t* partials,
                unsigned int* pdone, int K, int world, int rank, PeerTable pt) {
     extern __shared__ __align__(128) unsigned char peel_smem_raw[];
     DynShared& sh = *reinterpret_cast<DynShared*>(peel_smem_raw);
@@ -1226,41 +1213,48 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
     int* pre = reinterpret_cast<int*>(peel_smem_raw + sizeof(DynShared));   // [npan + 1]
     int* S = pre + npan + 1;                                        // [nq + 1] cost units before local pair lp
     const size_t cp_stride = (size_t)(K + 1) * PW;
-    unsigned int epoch = 0, ebase = 0;
-    if constexpr (MULTI) ebase = peer_state(pt, pt.rank)->epoch_base;
-    unsigned int* bar = reinterpret_cast<unsigned int*>(&scal->barrier);
+    // Front f of this launch carries epoch e0 + f.  One GPU: the host cleared the size words and the
+    // counter, epochs start at 1.  Fused multi-rank: both run on from launch to launch (every rank
+    // passes the same number of fronts), so stale words never validate and nothing is cleared.
+    unsigned int e0 = 1, abase = 0;
+    const unsigned int* arrived = &scal->arrived;
+    if constexpr (MULTI) {
+        e0 = peer_state(pt, pt.rank)->epoch_base + 1u;
+        abase = peer_state(pt, pt.rank)->arrived_base;
+        arrived = &peer_state(pt, pt.rank)->arrived;
+    }
+    const unsigned long long t_start = global_ns();
+    if (threadIdx.x == 0) { sh.pub.n = 0; sh.pub.extra = 0; }
+    __syncthreads();
 
     // ---- init: int counts -> planes, alive mask, front 0 ------------------------------------------
-    for (int lp = B; lp < nq; lp += G) {
-        const int Q = gpair(lp);
-        for (int c2 = threadIdx.x; c2 < 2 * TW; c2 += blockDim.x) {
-            const int h = c2 >> 10, c = c2 & (TW - 1), J = 2 * Q + h, l = 2 * lp + h;
-            const int j = J * TW + c;
-            uint32_t* cp = cplanes + (size_t)l * cp_stride;
-            const int v = (j < U) ? count[(size_t)l * TW + c] : 0;
-            for (int p = 0; p < K; ++p) {
-                const uint32_t w = __ballot_sync(0xFFFFFFFFu, (v >> p) & 1);
-                if (lane == 0) __stcg(cp + p * PW + (c >> 5), w);
+    {
+        FWord* seg0 = (e0 & 1u) ? segB : segA;
+        FWord* cnt0 = pcnt + (size_t)(e0 & 1u) * pstride;
+        for (int lp = B; lp < nq; lp += G) {
+            const int Q = gpair(lp);
+            for (int c2 = threadIdx.x; c2 < 2 * TW; c2 += blockDim.x) {
+                const int h = c2 >> 10, c = c2 & (TW - 1), J = 2 * Q + h, l = 2 * lp + h;
+                const int j = J * TW + c;
+                uint32_t* cp = cplanes + (size_t)l * cp_stride;
+                const int v = (j < U) ? count[(size_t)l * TW + c] : 0;
+                for (int p = 0; p < K; ++p) {
+                    const uint32_t w = __ballot_sync(0xFFFFFFFFu, (v >> p) & 1);
+                    if (lane == 0) __stcg(cp + p * PW + (c >> 5), w);
+                }
+                const uint32_t a = __ballot_sync(0xFFFFFFFFu, j < U);
+                if (lane == 0) __stcg(cp + K * PW + (c >> 5), a);
             }
-            const uint32_t a = __ballot_sync(0xFFFFFFFFu, j < U);
-            if (lane == 0) __stcg(cp + K * PW + (c >> 5), a);
+            __syncthreads();
+            if (warp < 2) {
+                const int J = 2 * Q + warp, l = 2 * lp + warp;
+                if (J < npan)
+                    peel_commit_seg<MULTI>(cplanes + (size_t)l * cp_stride, K, NoDelta{}, 0, lane, J, seg0, cnt0, e0,
+                                           rank_u + (size_t)l * TW, 0, pt, &sh.pub);
+            }
+            __syncthreads();
         }
-        __syncthreads();
-        if (warp < 2) {
-            const int J = 2 * Q + warp, l = 2 * lp + warp;
-            if (J < npan)
-                peel_commit_seg<MULTI>(cplanes + (size_t)l * cp_stride, K, NoDelta{}, 0, lane, J, segA, pcnt + J,
-                                       rank_u + (size_t)l * TW, 0, pt);
-        }
-        __syncthreads();
-    }
-    if constexpr (MULTI) {
-        if (world_barrier_seg(scal, epoch, ebase, pt, &sh.nf) < 0) {
-            if (B == 0 && threadIdx.x == 0) scal->fronts = -1;
-            return;
-        }
-    } else {
-        grid_barrier_plain(bar, epoch);
+        publish_pending<MULTI>(&sh.pub, cnt0, e0, scal, pt);
     }
 
     Ring2 rg;
@@ -1269,23 +1263,71 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
     unsigned long long t_acc = 0, t_mc = 0, t_bar = 0, t_mark = global_ns();
     for (;; ++k) {
         // ---- the front as a virtual list: pre[J] = members in panels < J; S[q] = cost units before pair q ----
-        const int* cnt = pcnt + (size_t)(k % 3) * pstride;
-        int* cnt_next = pcnt + (size_t)((k + 1) % 3) * pstride;
-        int* cnt_clear = pcnt + (size_t)((k + 2) % 3) * pstride;
-        for (int i = B * blockDim.x + threadIdx.x; i < npan; i += G * blockDim.x) cnt_clear[i] = 0;
-        // Scan 1: thread t owns the global pairs [t*ppt, (t+1)*ppt) - their panel counts in registers, one L2
+        const unsigned int fe = e0 + (unsigned int)k;              // this front's epoch
+        const FWord* cnt = pcnt + (size_t)(fe & 1u) * pstride;
+        FWord* cnt_next = pcnt + (size_t)((fe + 1u) & 1u) * pstride;
+        // Scan 1: thread t owns the global pairs [t*ppt, (t+1)*ppt) - their panel sizes in registers, one L2
         // round trip - and writes pre[].  Scan 2: thread t owns local pairs and writes S[] (cost units).
+        // Loading the sizes IS the synchronisation between fronts: a size word is valid once its owner has
+        // published the panel for this front (on whatever GPU).  Thread 0 first waits for the arrival
+        // counter (one word to poll), then the CTA re-reads the words until all of them are valid.
         {
             const int ppt = (nqg + PEEL_WARPS * 32 - 1) / (PEEL_WARPS * 32);    // <= DYN_MAX_PPT (host checks)
             const int q0 = threadIdx.x * ppt;
             int c[2 * DYN_MAX_PPT];
             int psum = 0;
-#pragma unroll
-            for (int i = 0; i < 2 * DYN_MAX_PPT; ++i) {
-                const int J = 2 * q0 + i;
-                c[i] = (i < 2 * ppt && J < npan) ? __ldcg(cnt + J) : 0;
-                psum += c[i];
+            bool done = false;
+            if (threadIdx.x == 0) {                                 // all npan panels of fronts 0..k published (hint)
+                const unsigned int target = abase + (unsigned int)npan * (unsigned int)(k + 1);
+                for (unsigned int spin = 0;; ++spin) {
+                    unsigned int v;
+                    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(arrived) : "memory");
+                    if ((int)(v - target) >= 0) break;
+                    if ((spin & 1023u) == 1023u && global_ns() - t_start > PEER_TIMEOUT_NS * (MULTI ? 1 : 8)) break;
+                }
+                asm volatile("fence.acq_rel.gpu;" ::: "memory");    // acquire: the committers' planes and members
             }
+            __syncthreads();
+            for (unsigned int round = 0;; ++round) {
+                bool ok = true;
+                psum = 0;
+#pragma unroll
+                for (int i = 0; i < 2 * DYN_MAX_PPT; ++i) {
+                    const int J = 2 * q0 + i;
+                    c[i] = 0;
+                    if (i < 2 * ppt && J < npan) {
+                        FWord w;
+                        asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(w) : "l"(cnt + J) : "memory");
+                        ok = ok && (unsigned int)(w >> 32) == fe;
+                        c[i] = (int)(unsigned int)w;
+                    }
+                    psum += c[i];
+                }
+                if (threadIdx.x == 0) {
+                    int dead = 0;
+                    if ((round & 255u) == 255u) {                   // a front never takes seconds: somebody is gone
+                        dead = global_ns() - t_start > PEER_TIMEOUT_NS * (MULTI ? 1 : 8);
+                        if constexpr (MULTI) {
+                            int ab;
+                            asm volatile("ld.relaxed.sys.global.s32 %0, [%1];" : "=r"(ab) : "l"(&peer_state(pt, pt.rank)->abort) : "memory");
+                            dead = dead || ab != 0;
+                        }
+                    }
+                    sh.dead = dead;
+                }
+                if (__syncthreads_and(ok)) { done = true; break; }
+                if (sh.dead) break;
+                __syncthreads();                                    // sh.dead is rewritten next round
+            }
+            if (!done) {
+                if constexpr (MULTI) {
+                    if ((int)threadIdx.x < pt.world)
+                        asm volatile("st.relaxed.sys.global.s32 [%0], %1;" ::"l"(&peer_state(pt, threadIdx.x)->abort), "r"(1) : "memory");
+                }
+                k = -1;
+                break;
+            }
+            if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_bar += t - t_mark; t_mark = t; }
             int incl = psum;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -1344,8 +1386,18 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
         if (nf <= 0) break;
         const long long T = S[nq];
         const int lo = (int)((long long)B * T / G), hi = (int)((long long)(B + 1) * T / G);
-        const int* seg = (k & 1) ? segB : segA;
-        int* seg_next = (k & 1) ? segA : segB;
+        const FWord* seg = (fe & 1u) ? segB : segA;
+        FWord* seg_next = (fe & 1u) ? segA : segB;
+        // Pairs the front does not reach (no member with a row stored for them) lose nothing and gain no
+        // member, but their panels' size words must still turn valid for the next front.  Nothing they
+        // depend on changed, so they go out at once, without a fence.
+        for (int t = B * blockDim.x + threadIdx.x; t < 2 * nq; t += G * blockDim.x) {
+            const int Q = gpair(t >> 1), J = 2 * Q + (t & 1);
+            if (J < npan && pre[min(2 * Q + 2, npan)] == 0) {
+                store_count<MULTI>(cnt_next + J, 0, fe + 1u, pt);
+                atomicAdd(&sh.pub.extra, 1);
+            }
+        }
         auto owner = [&](int u) {                                   // CTA whose range holds cost unit u
             return (int)((((long long)(u + 1) * G) + T - 1) / T) - 1;
         };
@@ -1373,7 +1425,7 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
                 const int npre = min(2 * Q + 2, npan);
                 const int rows = pre[npre];
                 Planes pa, pb;
-                peel_accumulate_groups(pre, npre, rows, seg, 0, gq, 0, 1, lane, bits + pair_words_before(lp, world, rank), rg, pa, pb);
+                peel_accumulate_groups(pre, npre, rows, seg, fe, 0, gq, 0, 1, lane, bits + pair_words_before(lp, world, rank), rg, pa, pb);
                 ring2_drain(rg, lane, pa, pb);
                 int pm = 1;
                 while ((1 << pm) <= rows) ++pm;                     // <= 8 planes: at most 128 rows
@@ -1384,7 +1436,7 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
                     const int J = 2 * Q + h, l = 2 * lp + h;
                     if (J < npan)
                         peel_commit_seg<MULTI>(cplanes + (size_t)l * cp_stride, K, SmemDelta{&sh.merge[warp][0][h * PW + lane]},
-                                               pm, lane, J, seg_next, cnt_next + J, rank_u + (size_t)l * TW, k + 1, pt);
+                                               pm, lane, J, seg_next, cnt_next, fe + 1u, rank_u + (size_t)l * TW, k + 1, pt, &sh.pub);
                 }
                 __syncwarp();
             }
@@ -1419,7 +1471,7 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
                 for (int gp = ga; gp < gb; gp += PASS_GROUPS) {
                     const int ge = min(gb, gp + PASS_GROUPS);
                     Planes pa, pb;
-                    peel_accumulate_groups(pre, npre, rows, seg, gp, ge, warp, PEEL_WARPS, lane, pbase, rg, pa, pb);
+                    peel_accumulate_groups(pre, npre, rows, seg, fe, gp, ge, warp, PEEL_WARPS, lane, pbase, rg, pa, pb);
                     ring2_drain(rg, lane, pa, pb);
                     const int per = ((ge - gp + PEEL_WARPS - 1) / PEEL_WARPS) << 5;   // rows a warp can have seen
                     int rp = 1;
@@ -1500,30 +1552,27 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
                     if (J < npan)
                         peel_commit_seg<MULTI>(cplanes + (size_t)l * cp_stride, K,
                                                SmemDelta{direct ? &sh.merge[0][0][warp * PW + lane] : &acc[0][warp * PW + lane]},
-                                               direct ? pm_last : pq, lane, J, seg_next, cnt_next + J, rank_u + (size_t)l * TW,
-                                               k + 1, pt);
+                                               direct ? pm_last : pq, lane, J, seg_next, cnt_next, fe + 1u,
+                                               rank_u + (size_t)l * TW, k + 1, pt, &sh.pub);
                 }
                 __syncthreads();
                 if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_mc += t - t_mark; t_mark = t; }
             }
         }
-        if constexpr (MULTI) {
-            if (world_barrier_seg(scal, epoch, ebase, pt, &sh.nf) < 0) { k = -1; break; }
-        } else {
-            grid_barrier_plain(bar, epoch);
-        }
-        if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_bar += t - t_mark; t_mark = t; }
+        publish_pending<MULTI>(&sh.pub, cnt_next, fe + 1u, scal, pt);
+        if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_mc += t - t_mark; t_mark = t; }
     }
     if constexpr (MULTI) {
-        // Exit barrier: once past it, no CTA of any rank reads this launch's front replica any more, so
-        // the next launch may push its front 0 without any host-level hand-shake.
-        if (k >= 0 && world_barrier_seg(scal, epoch, ebase, pt, &sh.nf) < 0) k = -1;
-        if (B == 0 && threadIdx.x == 0) peer_state(pt, pt.rank)->epoch_base = ebase + epoch;
+        // k + 1 fronts (the last one empty) were published by every rank: the next launch continues from there
+        if (B == 0 && threadIdx.x == 0 && k >= 0) {
+            peer_state(pt, pt.rank)->epoch_base = e0 + (unsigned int)k;
+            peer_state(pt, pt.rank)->arrived_base = abase + (unsigned int)npan * (unsigned int)(k + 1);
+        }
     }
     if (B == 0 && threadIdx.x == 0) scal->fronts = k;
     if (threadIdx.x == 0 && (B == 0 || B == G - 1)) {
         unsigned long long* d = scal->dbg + (B == 0 ? 0 : 4);
-        d[0] = t_acc; d[1] = t_mc; d[2] = t_bar; d[3] = (unsigned long long)k;
+        d[0] = t_acc; d[1] = t_mc; d[2] = t_bar; d[3] = (unsigned long long)(k > 0 ? k : 1);
     }
 }
 
@@ -1693,7 +1742,7 @@ static int apply(const Plan& P, int k, const uint32_t* masks, int* any_out, cuda
 // Peer-mapped buffer of the fused multi-rank peel: [PeerState | counts 3 x stride | pad | segments A | segments B]
 static int peer_cnt_stride(const Layout& L) { return L.np + 2; }
 static size_t peer_seg_offset(const Layout& L) {
-    return align_up(sizeof(PeerState) + sizeof(int) * 3 * (size_t)(L.np + 2), 256);
+    return align_up(sizeof(PeerState) + sizeof(FWord) * 2 * (size_t)(L.np + 2), 256);
 }
 
 static size_t peel_smem_bytes(const Layout& L) {
@@ -1736,21 +1785,21 @@ static int peel_persistent(const Plan& P, cudaStream_t s, const PeerTable* peers
     uint32_t* partials = P.at<uint32_t>(L.partials);
     unsigned int* pdone = P.at<unsigned int>(L.pdone);
     int K = L.kplanes, ps = peer_cnt_stride(L), world = L.world, rank = L.rank;
-    int *pcnt, *fa, *fb;
+    FWord *pcnt, *fa, *fb;
     PeerTable pt{};
     if (peers) {
         // front segments and per-panel counts live in the peer-mapped buffer (every rank holds all panels);
         // evx_nds_shard_peer_init cleared it once and every launch leaves the counts cleared
         pt = *peers;
         char* mine = pt.base[L.rank];
-        pcnt = reinterpret_cast<int*>(mine + sizeof(PeerState));
-        fa = reinterpret_cast<int*>(mine + peer_seg_offset(L));
+        pcnt = reinterpret_cast<FWord*>(mine + sizeof(PeerState));
+        fa = reinterpret_cast<FWord*>(mine + peer_seg_offset(L));
         fb = fa + L.npad;
     } else {
-        pcnt = P.at<int>(L.pcnt);
-        fa = P.at<int>(L.flist);
-        fb = P.at<int>(L.flist2);
-        EVX_CUDA(cudaMemsetAsync(pcnt, 0, sizeof(int) * 3 * (size_t)ps, s));
+        pcnt = P.at<FWord>(L.pcnt);
+        fa = P.at<FWord>(L.flist);
+        fb = P.at<FWord>(L.flist2);
+        EVX_CUDA(cudaMemsetAsync(pcnt, 0, sizeof(FWord) * 2 * (size_t)ps, s));     // epoch 0 = never valid
     }
     void* args[] = {&bits, &count, &rank_u, &fa, &fb, &scal, &cpl, &pcnt, &ps, &partials, &pdone, &K, &world, &rank, &pt};
     EVX_CUDA(cudaLaunchCooperativeKernel(dk, dim3(dgrid), dim3(PEEL_WARPS * 32), args, dyn_smem, s));
@@ -1862,13 +1911,13 @@ extern "C" int evx_nds_shard_ranks(evx_nds_shard* p, int32_t* rank_partial, void
 extern "C" size_t evx_nds_shard_peer_bytes(const evx_nds_shard* p) {
     if (!p) return 0;
     const Layout& L = p->P.L;
-    return peer_seg_offset(L) + 2 * sizeof(int) * (size_t)L.npad;
+    return peer_seg_offset(L) + 2 * sizeof(FWord) * (size_t)L.npad;
 }
 
 extern "C" int evx_nds_shard_peer_init(evx_nds_shard* p, void* local_peer_buf, void* stream) {
     EVX_REQUIRE(p && local_peer_buf, EVX_ERR_ARG, "evx_nds_shard_peer_init: null argument");
-    // message words, epoch base and per-panel counts; segments need no clearing (the counts bound every read)
-    EVX_CUDA(cudaMemsetAsync(local_peer_buf, 0, peer_seg_offset(p->P.L), (cudaStream_t)stream));
+    // epoch base, counter, abort flag and every front word: epoch 0 never validates
+    EVX_CUDA(cudaMemsetAsync(local_peer_buf, 0, evx_nds_shard_peer_bytes(p), (cudaStream_t)stream));
     return EVX_OK;
 }
 
@@ -1912,7 +1961,8 @@ extern "C" int evx_debug_peel_times(evx_nds_shard* p, uint64_t* out8) {
         return EVX_OK;
     }
     Scal* scal = p->P.at<Scal>(p->P.L.scal);
-    EVX_CUDA(cudaMemcpy(out8, scal->dbg, sizeof(uint64_t) * 16, cudaMemcpyDeviceToHost));
+    memset(out8, 0, sizeof(uint64_t) * 16);
+    EVX_CUDA(cudaMemcpy(out8, scal->dbg, sizeof(uint64_t) * 8, cudaMemcpyDeviceToHost));
     return EVX_OK;
 }
 
@@ -1996,7 +2046,7 @@ extern "C" int evx_nds_f32(const float* x, int64_t n, int32_t m, int32_t* rank, 
         EVX_CUDA(cudaEventElapsedTime(&pf.prep_ms, pf.ev[0], pf.ev[1]));
         EVX_CUDA(cudaEventElapsedTime(&pf.tiles_ms, pf.ev[1], pf.ev[2]));
         EVX_CUDA(cudaEventElapsedTime(&pf.peel_ms, pf.ev[2], pf.ev[3]));
-        EVX_CUDA(cudaMemcpy(g_dbg_times, scal->dbg, sizeof(g_dbg_times), cudaMemcpyDeviceToHost));
+        EVX_CUDA(cudaMemcpy(g_dbg_times, scal->dbg, sizeof(uint64_t) * 8, cudaMemcpyDeviceToHost));
         pf.have = true;
     }
     return EVX_OK;

@@ -167,18 +167,18 @@ int evx_nds_shard_detect(evx_nds_shard* p, int32_t k, uint32_t* local_mask, void
 int evx_nds_shard_apply(evx_nds_shard* p, int32_t k, const uint32_t* all_masks, int32_t* any_out,
                         void* stream);
 /* Fused alternative to the detect / all-gather / apply loop: ONE persistent kernel per rank peels
- * every front.  Every rank holds a replica of the current front (per-panel member lists) in peer-mapped
- * memory; the warp that finds a panel's new members stores them straight into every rank's replica over
- * NVLink (plain peer stores, no cross-GPU atomics), and a barrier over all CTAs of all ranks separates
- * the fronts: local arrival counter, one 64-bit message per rank pair, every CTA polls its own GPU's
- * message words.  Each rank provides `peer_bytes` of peer-mapped memory (e.g. torch symmetric memory);
- * peer_bufs[r] (HOST array of world device pointers) is rank r's buffer as mapped in this process.
+ * every front.  Every rank holds a replica of the current front (per-panel member lists and sizes, as
+ * 64-bit words tagged with the front's epoch) in peer-mapped memory; the warp that finds a panel's new
+ * members stores them straight into every rank's replica over NVLink (plain 8-byte peer stores: no
+ * cross-GPU atomics on data, no system-scope fences).  There is no barrier between fronts: a CTA starts
+ * the next front when every panel's size word carries that front's epoch.  Each rank provides
+ * `peer_bytes` of peer-mapped memory (e.g. torch symmetric memory); peer_bufs[r] (HOST array of world
+ * device pointers) is rank r's buffer as mapped in this process.
  * Sequence: peer_init ONCE per plan -> host-level barrier across ranks -> then, per population,
- * build -> peel_fused -> ranks, with no further hand-shake between calls (barrier epochs continue
- * across launches and every launch ends with a barrier).  num_fronts == NULL: asynchronous, the front
- * count is available from evx_nds_last_num_fronts(); otherwise the call waits and fails with a message
- * (never hangs) if a rank was more than 4 s late - after which peer_init + host barrier are needed
- * again.  world <= 8, n <= 2M.                                                                       */
+ * build -> peel_fused -> ranks, with no further hand-shake between calls (epochs continue across
+ * launches).  num_fronts == NULL: asynchronous, the front count is available from
+ * evx_nds_last_num_fronts(); otherwise the call waits and fails with a message (never hangs) if a rank
+ * was more than 4 s late - after which peer_init + host barrier are needed again.  world <= 8, n <= 2M. */
 size_t evx_nds_shard_peer_bytes(const evx_nds_shard* p);
 int evx_nds_shard_peer_init(evx_nds_shard* p, void* local_peer_buf, void* stream);
 int evx_nds_shard_peel_fused(evx_nds_shard* p, void* const* peer_bufs, int32_t* num_fronts, void* stream);
@@ -194,11 +194,10 @@ void evx_launch_count_reset(void);
  * this host thread while enabled: sort+unique, dominance tile kernel, front peeling.              */
 void evx_profile_enable(int32_t on);
 int evx_profile_last(float* prep_ms, float* tiles_ms, float* peel_ms);
-/* nanoseconds the persistent peel kernel of the plan's last run spent in {accumulate, merge+commit,
- * barrier, fronts} as seen by its first CTA (out16[0..3]) and its last CTA (out16[4..7]); out16[8..10]:
- * steps of the multi-rank barrier as seen by CTA 0 (fence + arrive, waiting for every rank's message,
- * acquire fence), summed over fronts.  p == NULL: the values of this host thread's last
- * evx_nds_f32 call made with evx_profile_enable(1).                                                 */
+/* nanoseconds the persistent peel kernel of the plan's last run spent in {gathering, merge + commit +
+ * publish, waiting for the next front's sizes, number of fronts} as seen by its first CTA (out16[0..3])
+ * and its last CTA (out16[4..7]); out16[8..15] are zero.  p == NULL: the values of this host thread's
+ * last evx_nds_f32 call made with evx_profile_enable(1).                                            */
 int evx_debug_peel_times(evx_nds_shard* p, uint64_t* out16);
 /* register-only issue-rate probe: runs `iters` dependent-free compare+logic steps per thread on
  * the whole chip and returns the measured pair-tests per second for the inner step the dominance

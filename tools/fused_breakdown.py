@@ -21,11 +21,8 @@ for _ in range(R):
     ev[0].record()
     f.shard.build(x)
     ev[1].record()
-    check(L.evx_nds_shard_peer_init(f.shard.plan, f.peer.data_ptr(), stream_ptr()))
-    torch.cuda.current_stream().synchronize()
-    dist.barrier()
     ev[2].record()
-    check(L.evx_nds_shard_peel_fused(f.shard.plan, f._ptrs, ctypes.byref(f._nf), stream_ptr()))
+    check(L.evx_nds_shard_peel_fused(f.shard.plan, f._ptrs, None, stream_ptr()))
     ev[3].record()
     f.shard.ranks(f.out)
     ev[4].record()
@@ -36,15 +33,12 @@ for _ in range(R):
 acc /= R
 t = torch.tensor(acc, device="cuda"); mx = t.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX); mn = t.clone(); dist.all_reduce(mn, op=dist.ReduceOp.MIN)
 if rank == 0:
-    names = ["build(sort+tiles)", "init+host barrier", "fused peel kernel", "rank scatter", "all_reduce ranks"]
+    names = ["build(sort+tiles)", "(nothing)", "fused peel kernel", "rank scatter", "all_reduce ranks"]
     for nm, a, b in zip(names, mn.tolist(), mx.tolist()): print(f"{nm:22s} min {a:8.3f} ms  max {b:8.3f} ms")
     dbg = (ctypes.c_uint64 * 16)()
     check(L.evx_debug_peel_times(f.shard.plan, dbg))
     for nm, o in (("first CTA", 0), ("last CTA", 4)):
         k = max(1, dbg[o + 3])
-        print(f"{nm}: per front  accumulate {dbg[o]/k/1e3:7.2f} us  merge+commit {dbg[o+1]/k/1e3:6.2f} us  barrier {dbg[o+2]/k/1e3:6.2f} us")
-    k = max(1, dbg[3])
-    names2 = ["own arrive", "local wait", "push to peers", "fence.sys+send", "peer wait", "fence.sys(acq)", "release"]
-    print("world barrier, CTA 0, us per front: " + ", ".join(f"{n} {dbg[8+i]/k/1e3:.2f}" for i, n in enumerate(names2)))
+        print(f"{nm}: per front  accumulate {dbg[o]/k/1e3:7.2f} us  merge+commit {dbg[o+1]/k/1e3:6.2f} us  wait for next front {dbg[o+2]/k/1e3:6.2f} us")
     print("fronts", f.num_fronts, "world", world, "n", n, flush=True)
 dist.destroy_process_group()
