@@ -20,10 +20,9 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
-# DRAM bytes per launch at N = 1M, M = 3 from ncu (profiles/r1_final_traffic_n1m.csv): read + write
-TILE_TRAFFIC_N1M = 64.85e9
-PEEL_TRAFFIC_N1M = 63.89e9
-TRAFFIC_SOURCE = "profiles/r1_final_traffic_n1m.csv (dram__bytes_read.sum + dram__bytes_write.sum per launch)"
+# ncu figures for the kernels at HEAD (DRAM bytes per launch at N = 1M, M = 3; issue-slot utilisation and
+# warp instructions per tested pair) live in this file, written from the ncu captures under profiles/
+NCU_SUMMARY = ROOT / "profiles" / "r2_ncu_summary.json"
 GATHER_PEAK_256B = 6760.0      # GB/s, random 256-byte rows through the peel's own ring (profiles/r1_gather_probe.txt)
 METRIC = "nd_sort_pairs_per_s"
 UNIT = "pairs/s"
@@ -37,6 +36,11 @@ def parse():
     ap.add_argument("--n", "--rows", dest="n", type=int, default=1_000_000)
     ap.add_argument("--m", type=int, default=3)
     ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--dist", default="uniform", choices=["uniform", "one_front", "chain"],
+                    help="input distribution (SURVEY 8d): i.i.d. uniform, one front (points on the simplex, a converged "
+                         "population), chain (n fronts of one row; n <= 20000)")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the side measurements (other seeds, one-front inputs, NSGA-II, operators)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-sample", type=int, default=0, help="rows of the CPU-baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -48,8 +52,24 @@ def parse():
     return ap.parse_args()
 
 
-def workload_name(n, m):
-    return f"non_dominated_sort N={n} M={m} uniform-random float32 (BASELINE.json configs[4] shape)"
+def workload_name(n, m, dist="uniform"):
+    kind = {"uniform": "uniform-random", "one_front": "one-front (simplex)", "chain": "chain"}[dist]
+    return f"non_dominated_sort N={n} M={m} {kind} float32 (BASELINE.json configs[4] shape)"
+
+
+def make_input(n, m, seed, dist="uniform"):
+    """Synthetic objectives.  uniform: rng.random((n, m)); one_front: the same rows scaled onto
+    the simplex sum(f) = 1 (a converged population: one front, up to rounding); chain: f_i = (i, .., i),
+    shuffled (n fronts of one row each)."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    x = rng.random((n, m), dtype=np.float32)
+    if dist == "one_front":
+        x = (x / x.sum(1, keepdims=True)).astype(np.float32)
+    elif dist == "chain":
+        assert n <= 20000, "chain has n fronts: small n only"
+        x = (np.arange(n, dtype=np.float32)[:, None] * np.ones((1, m), np.float32))[rng.permutation(n)]
+    return x
 
 
 # ------------------------------------------------------------------------------------------------
@@ -194,7 +214,7 @@ def run_ours(args):
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
 
-    x_host = torch.from_numpy(np.random.default_rng(args.seed).random((n, m), dtype=np.float32)).pin_memory()
+    x_host = torch.from_numpy(make_input(n, m, args.seed, args.dist)).pin_memory()
     x = x_host.cuda(non_blocking=True)
     stream = torch.cuda.current_stream()
 
@@ -284,6 +304,9 @@ def run_ours(args):
         ms_e2e = timed(step_e2e, K)
         verified = verify_last_step(torch, dist, x, holder["r"], world, rank, args.verify_rows)
 
+    nsga2_multi = None
+    if world > 1 and not args.no_nsga2 and not args.no_extras:
+        nsga2_multi = nsga2_gens_per_s(torch, dist=dist, exchange=args.exchange)          # every rank takes part
     if not verified["ok"]:
         if rank == 0:
             print(json.dumps({"metric": METRIC, "error": "ranks of the last timed step failed the sampled exactness check",
@@ -300,7 +323,7 @@ def run_ours(args):
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": workload_name(n, m), "fronts": fronts, "parallelism": f"column-panel shards x{world}" + (f", front exchange: {args.exchange}" if world > 1 else ""),
+            "config": {"workload": workload_name(n, m, args.dist), "seed": args.seed, "fronts": fronts, "parallelism": f"column-panel shards x{world}" + (f", front exchange: {args.exchange}" if world > 1 else ""),
                        "l2": "working set (packed bit matrix %.1f GB) >> 126 MB L2; no flush needed" % (n * n / 16 / 1e9)},
             "clocks": clocks, "gpu_launches": launches, "verified": verified,
             "e2e": {"value": pairs * K / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": n * m * 4,
@@ -313,41 +336,44 @@ def run_ours(args):
         headline = (n == 1_000_000 and m == 3)        # the ncu DRAM counters in profiles/ are for this shape
         line["roofline"] = {"bound": "hbm", "kernel": "k_dominance_tiles", "achieved": alg_bytes / t / 1e9, "peak": hbm_peak,
                             "unit": "GB/s", "frac": alg_bytes / t / 1e9 / hbm_peak,
-                            "traffic": TILE_TRAFFIC_N1M if headline else None,
-                            "traffic_source": TRAFFIC_SOURCE if headline else None,
+                            "traffic": None, "traffic_source": None,
                             "reference_equivalent": {"bytes": pairs / 8.0, "GB/s": pairs / 8.0 / t / 1e9,
                                                      "note": "one bit for every one of the reference's N^2 ordered pairs"},
                             "peak_source": peak_src, "ms_per_launch": stages["tiles"],
                             "note": "algorithmic bytes = N^2/16: 1 bit written per tested pair, N^2/2 pairs tested per launch; "
-                                    "what limits the kernel is instruction issue (85 % of the issue slots, profiles/), not "
-                                    "HBM: see compare_roofline"}
+                                    "what limits the kernel is instruction issue, not HBM: see issue_roofline"}
         tp = stages["peel"] * 1e-3
         peel_bytes = pairs / 16.0                     # every stored bit is read exactly once by the peel
         line["peel_roofline"] = {"bound": "hbm", "kernel": "k_peel_dynamic", "achieved": peel_bytes / tp / 1e9,
                                  "peak": hbm_peak, "unit": "GB/s", "frac": peel_bytes / tp / 1e9 / hbm_peak,
-                                 "traffic": PEEL_TRAFFIC_N1M if headline else None, "ms_per_launch": stages["peel"],
+                                 "traffic": None, "ms_per_launch": stages["peel"],
                                  "random_gather_peak": GATHER_PEAK_256B,
                                  "frac_of_random_gather_peak": peel_bytes / tp / 1e9 / GATHER_PEAK_256B,
                                  "note": "random gather of 256-byte super-rows through a cp.async ring: "
                                          "tools/probes/gather_probe4.cu measures 6.76 TB/s for exactly this ring and consumer "
-                                         "(profiles/r1_gather_probe.txt); the rest is per-front latency (about 230 fronts, "
-                                         "one grid barrier each)"}
+                                         "(profiles/r1_gather_probe.txt); the rest is per-front latency (about 230 fronts)"}
         line["stages_ms"] = stages
+        ncu = {}
         try:
-            pr = ctypes.c_double()
-            check(L.evx_probe_compare_rate(3 if m != 10 else 10, 2000, ctypes.byref(pr), stream.cuda_stream))
-            issued_pairs = pairs / 2.0                # the strict upper triangle is what the kernel tests
-            line["compare_roofline"] = {"bound": "alu-issue", "peak_pairs_per_s": pr.value, "peak_source":
-                                        "evx_probe_compare_rate (register-only inner step, measured this run)",
-                                        "achieved_tested_pairs_per_s": issued_pairs / t,
-                                        "frac": issued_pairs / t / pr.value,
-                                        "algorithmic_pairs_per_s": pairs / t}
-        except Exception as e:                        # probe only supports m in {3, 10}
-            line["compare_roofline"] = {"error": str(e)}
-    if world == 1 and not args.no_nsga2:
-        line["nsga2"] = nsga2_gens_per_s(torch)
-        line["nsga2_small"] = nsga2_gens_per_s(torch, pop=100, d=7, m=3, gens=100, problem="DTLZ1")   # configs[0] shape
+            ncu = json.loads(NCU_SUMMARY.read_text())
+        except Exception:
+            pass
+        if headline and ncu:
+            line["roofline"]["traffic"] = ncu.get("tiles_dram_bytes_per_launch")
+            line["roofline"]["traffic_source"] = ncu.get("source")
+            line["peel_roofline"]["traffic"] = ncu.get("peel_dram_bytes_per_launch")
+        if ncu.get("tiles_issue"):
+            # the tile kernel is bound by instruction issue: report what ncu measured for it, not a synthetic peak
+            line["issue_roofline"] = dict(ncu["tiles_issue"], kernel="k_dominance_tiles", source=ncu.get("source"),
+                                          tested_pairs_per_s=pairs / 2.0 / t, algorithmic_pairs_per_s=pairs / t)
+    if nsga2_multi is not None:
+        line["nsga2"] = nsga2_multi
+    if world == 1 and not args.no_extras:
+        if not args.no_nsga2:
+            line["nsga2"] = nsga2_gens_per_s(torch)
+            line["nsga2_small"] = nsga2_gens_per_s(torch, pop=100, d=7, m=3, gens=100, problem="DTLZ1")   # configs[0] shape
         line["operators"] = operator_rates(torch, hbm_peak)
+        line["other_inputs"] = other_inputs(torch, L, n, m, args)
     if not args.no_cpu_baseline:
         ns = auto_cpu_sample(m, args.seed, user=args.cpu_sample)
         _, dt1, _ = cpu_oracle_rate(ns, m, args.seed)
@@ -402,27 +428,81 @@ def operator_rates(torch, hbm_peak):
     return out
 
 
-def nsga2_gens_per_s(torch, pop=100_000, d=12, m=3, gens=10, problem="DTLZ2"):
+def other_inputs(torch, L, n, m, args):
+    """the same sort on seeds {0, 1, 2} and on the structured inputs that drive the peel
+    differently (one front = a converged NSGA-II population), ms per sort, 3 timed calls after 2 warm-ups."""
+    from evox_b200._lib import check
+    out = {}
+    ws = torch.empty(L.evx_nds_workspace_bytes(n, m), dtype=torch.uint8, device="cuda")
+    s = torch.cuda.current_stream().cuda_stream
+    cases = [("uniform", sd, n) for sd in (0, 1, 2)] + [("one_front", 0, n)]
+    if n != 200_000:
+        cases += [("uniform", 0, 200_000), ("one_front", 0, 200_000)]
+    for dist, seed, nn in cases:
+        x = torch.from_numpy(make_input(nn, m, seed, dist)).cuda()
+        r = torch.empty(nn, dtype=torch.int32, device="cuda")
+
+        def call():
+            check(L.evx_nds_f32(x.data_ptr(), nn, m, r.data_ptr(), ws.data_ptr(), ws.numel(), s))
+        for _ in range(2):
+            call()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(3):
+            call()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 3
+        out[f"{dist}_seed{seed}_n{nn}"] = {"ms": ms, "pairs_per_s": float(nn) ** 2 / (ms * 1e-3), "fronts": int(r.max()) + 1}
+    return out
+
+
+def nsga2_gens_per_s(torch, pop=100_000, d=12, m=3, gens=50, problem="DTLZ2", dist=None, exchange="fused"):
     """Second half of BASELINE.json's metric: NSGA-II generations/s at pop 100k on DTLZ2 (configs[2]):
-    variation kernel -> DTLZ2 evaluate -> concat -> non_dominate(2*pop -> pop), all on the device."""
+    variation kernel -> DTLZ2 evaluate -> concat -> survivor selection (merged N = 2 pop -> pop), all on the
+    device, >= 50 generations after 3 of warm-up.  With several GPUs (dist given): state
+    replicated, evaluation sharded by rows + all-gather of the fitness, the sort sharded by column panels
+    (evox_b200.distributed.ShardedNSGA2); timed between barriers, max over ranks."""
     import evox_b200 as E
     from evox_b200.algorithms import NSGA2, run_generations
     alg = NSGA2(torch.zeros(d), torch.ones(d), n_objs=m, pop_size=pop)
     prob = getattr(E.problems.numerical, problem)(d=d, m=m)
-    state = alg.setup(seed=0)
-    state, _ = run_generations(alg, prob, state, 3)                    # warm-up (first fronts are the deepest)
+    world = dist.get_world_size() if dist is not None else 1
+    if world > 1:
+        from evox_b200.distributed import ShardedNSGA2
+        drv = ShardedNSGA2(alg, exchange=exchange)
+        run = lambda st, g: drv.run(prob, st, g)[0]
+    else:
+        run = lambda st, g: run_generations(alg, prob, st, g)[0]
+    state = run(alg.setup(seed=0), 3)                                    # warm-up (first fronts are the deepest)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize()
     e0.record()
-    state, _ = run_generations(alg, prob, state, gens)
+    state = run(state, gens)
     e1.record()
     torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1)
-    return {"metric": "nsga2_generations_per_s", "value": gens / (ms * 1e-3), "unit": "generations/s",
+    if world > 1:
+        dist.barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+    chk = torch.tensor([float(state.fitness.double().sum())], device="cuda", dtype=torch.float64)
+    same = True
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        lo, hi = chk.clone(), chk.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        same = bool((lo == hi).all())
+    ms = float(ms)
+    return {"metric": "nsga2_generations_per_s", "value": gens / (ms * 1e-3), "unit": "generations/s", "n_gpus": world,
             "ms_per_generation": ms / gens, "config": {"workload": f"NSGA-II {problem} d={d} M={m} pop={pop} (merged N={2 * pop})",
                                                        "generations_timed": gens, "after_warmup_generations": 3},
-            "note": "variation = evx_variation_sbx_pm_f32 (Philox; statistical parity with jax.random), "
-                    "selection glue = torch sorts as in non_dominate.py:210-222"}
+            "population_identical_on_all_gpus": same, "fitness_checksum": float(chk),
+            "note": "variation = evx_variation_sbx_pm_f32 (Philox; value parity with the reference's operators for a given "
+                    "draw), selection = evx_non_dominate_f32 / evx_select_by_rank_f32 (non_dominate.py:210-222 as one call)"}
 
 
 def main():

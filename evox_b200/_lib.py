@@ -27,6 +27,7 @@ _SIGNATURES = {
     "evx_crowding_distance_sort_f32": (ctypes.c_int, [c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_sz, c_vp]),
     "evx_non_dominate_workspace_bytes": (c_sz, [c_i64, c_i32]),
     "evx_non_dominate_f32": (ctypes.c_int, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_i64, c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "evx_select_by_rank_f32": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_i64, c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
     "evx_eval_dtlz_f32": (ctypes.c_int, [c_i32, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp]),
     "evx_eval_maf1_f32": (ctypes.c_int, [c_vp, c_i64, c_i32, c_i32, c_vp, c_vp]),
     "evx_lsmop_groups": (ctypes.c_int, [c_i32, c_i32, c_vp, c_vp]),
@@ -50,7 +51,6 @@ _SIGNATURES = {
     "evx_launch_count_reset": (None, []),
     "evx_profile_enable": (None, [c_i32]),
     "evx_profile_last": (ctypes.c_int, [ctypes.POINTER(ctypes.c_float)] * 3),
-    "evx_probe_compare_rate": (ctypes.c_int, [c_i32, c_i64, ctypes.POINTER(ctypes.c_double), c_vp]),
 }
 
 

@@ -1,4 +1,4 @@
-// api.cu - error plumbing, launch accounting, host-entry arena, issue-rate probe.
+// api.cu - error plumbing, launch accounting, host-entry arena.
 #include <mutex>
 
 #include "common.cuh"
@@ -49,42 +49,6 @@ int arena_get(size_t bytes, void** ptr) {
     return EVX_OK;
 }
 
-// Register-only probe of the tile kernel's inner step: per 32 pair tests a warp issues (M-1)
-// FSETP and one predicated bit-set.  No memory traffic; values come from the thread index so the
-// compiler cannot fold the loop.  pair tests = threads * iters * 32 (columns per word) * RB.
-template <int MM>
-__global__ void k_probe(float seed, int64_t iters, uint32_t* sink) {
-    float xi[4][MM];
-    float cv[32][MM > 0 ? MM : 1];
-#pragma unroll
-    for (int q = 0; q < 4; ++q)
-#pragma unroll
-        for (int k = 0; k < MM; ++k) xi[q][k] = seed * (float)(threadIdx.x + 3 * q + k);
-    uint32_t acc = 0;
-    float drift = seed;
-    for (int64_t it = 0; it < iters; ++it) {
-        uint32_t w[4] = {0, 0, 0, 0};
-#pragma unroll
-        for (int b = 0; b < 32; ++b) {
-#pragma unroll
-            for (int k = 0; k < MM; ++k) cv[b][k] = drift + (float)(b * 7 + k);
-        }
-#pragma unroll
-        for (int b = 0; b < 32; ++b) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                bool p = true;
-#pragma unroll
-                for (int k = 0; k < MM; ++k) p = p && (xi[q][k] <= cv[b][k]);
-                if (p) w[q] |= 1u << b;
-            }
-        }
-        acc ^= w[0] ^ (w[1] << 1) ^ (w[2] >> 1) ^ (w[3] << 3);
-        drift += 1.0f;
-    }
-    if (acc == 0x12345678u) sink[0] = acc;
-}
-
 }  // namespace evx
 
 using namespace evx;
@@ -93,34 +57,3 @@ extern "C" int evx_version(void) { return 100; }
 extern "C" const char* evx_last_error(void) { return last_error_buf(); }
 extern "C" int64_t evx_launch_count(void) { return launch_counter(); }
 extern "C" void evx_launch_count_reset(void) { launch_counter() = 0; }
-
-extern "C" int evx_probe_compare_rate(int32_t m, int64_t iters, double* pairs_per_s, void* stream) {
-    EVX_REQUIRE(pairs_per_s && iters > 0, EVX_ERR_ARG, "evx_probe_compare_rate: bad argument");
-    EVX_REQUIRE(m == 3 || m == 10, EVX_ERR_ARG, "evx_probe_compare_rate: m must be 3 or 10");
-    cudaStream_t s = (cudaStream_t)stream;
-    int dev = 0, sms = 0;
-    EVX_CUDA(cudaGetDevice(&dev));
-    EVX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    std::lock_guard<std::recursive_mutex> hold(arena_mutex());
-    uint32_t* sink = nullptr;
-    int rc = arena_get(256, reinterpret_cast<void**>(&sink));
-    if (rc) return rc;
-    cudaEvent_t e0, e1;
-    EVX_CUDA(cudaEventCreate(&e0));
-    EVX_CUDA(cudaEventCreate(&e1));
-    const int blocks = sms * 8, threads = 256;
-    for (int rep = 0; rep < 2; ++rep) {
-        EVX_CUDA(cudaEventRecord(e0, s));
-        if (m == 3) k_probe<2><<<blocks, threads, 0, s>>>(1.0f, iters, sink);
-        else k_probe<9><<<blocks, threads, 0, s>>>(1.0f, iters, sink);
-        EVX_LAUNCH_CHECK();
-        EVX_CUDA(cudaEventRecord(e1, s));
-        EVX_CUDA(cudaEventSynchronize(e1));
-    }
-    float ms = 0.f;
-    EVX_CUDA(cudaEventElapsedTime(&ms, e0, e1));
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
-    *pairs_per_s = (double)blocks * threads * (double)iters * 32.0 * 4.0 / (ms * 1e-3);
-    return EVX_OK;
-}

@@ -163,23 +163,11 @@ extern "C" size_t evx_non_dominate_workspace_bytes(int64_t n, int32_t m) {
     return sel_layout(n, m).total + 256;
 }
 
-extern "C" int evx_non_dominate_f32(const float* pop, const float* fit, const float* fit_out_src, int64_t n, int32_t d,
-                                    int32_t m, int64_t topk, float* out_pop, float* out_fit, int32_t* out_index,
-                                    void* ws, size_t ws_bytes, void* stream) {
-    EVX_REQUIRE(n >= 1 && m >= 1 && m <= EVX_MAX_OBJECTIVES && d >= 0, EVX_ERR_ARG,
-                "evx_non_dominate_f32: bad shape n=%lld d=%d m=%d", (long long)n, d, m);
-    EVX_REQUIRE(topk >= 1 && topk <= n, EVX_ERR_ARG, "evx_non_dominate_f32: topk=%lld must be in [1, n=%lld]",
-                (long long)topk, (long long)n);
-    EVX_REQUIRE(fit && (out_pop == nullptr || (pop && d > 0)) && (out_pop || out_fit || out_index), EVX_ERR_ARG,
-                "evx_non_dominate_f32: null pointer");
-    const size_t need = evx_non_dominate_workspace_bytes(n, m);
-    EVX_REQUIRE(need != 0, EVX_ERR_ARG, "evx_non_dominate_f32: n=%lld too large", (long long)n);
-    EVX_REQUIRE(ws && ws_bytes >= need, EVX_ERR_WORKSPACE, "evx_non_dominate_f32: workspace %zu < required %zu", ws_bytes,
-                need);
-    cudaStream_t s = (cudaStream_t)stream;
-    char* base = reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(ws), 256));
-    const SelLayout L = sel_layout(n, m);
-    int* rank = reinterpret_cast<int*>(base + L.rank);
+// Everything after the ranks: cut rank, crowding permutation, final order, gather.  `rank` may live
+// anywhere; `inner` is scratch for the crowding sort.
+static int select_by_rank(const float* pop, const float* fit, const float* fit_out_src, const int* rank, int64_t n, int d,
+                          int m, int64_t topk, float* out_pop, float* out_fit, int32_t* out_index, char* base,
+                          const SelLayout& L, cudaStream_t s) {
     int* hist = reinterpret_cast<int*>(base + L.hist);
     SelScal* sc = reinterpret_cast<SelScal*>(base + L.sc);
     uint8_t* mask = reinterpret_cast<uint8_t*>(base + L.mask);
@@ -190,9 +178,6 @@ extern "C" int evx_non_dominate_f32(const float* pop, const float* fit, const fl
     int* vB = reinterpret_cast<int*>(base + L.valsB);
     const int T = 256;
     const unsigned gn = (unsigned)ceil_div(n, T);
-
-    int rc = evx_nds_f32(fit, n, m, rank, base + L.inner, L.inner_bytes, stream);                       // :211
-    if (rc) return rc;
     EVX_CUDA(cudaMemsetAsync(hist, 0, sizeof(int) * (size_t)(n + 1), s));
     EVX_CUDA(cudaMemsetAsync(sc, 0, sizeof(SelScal), s));
     k_sel_hist<<<gn, T, 0, s>>>(rank, n, hist, sc);
@@ -201,15 +186,54 @@ extern "C" int evx_non_dominate_f32(const float* pop, const float* fit, const fl
     EVX_LAUNCH_CHECK();
     k_sel_mask<<<gn, T, 0, s>>>(rank, n, sc, mask);                                                     // :215
     EVX_LAUNCH_CHECK();
-    rc = crowding_sort_known(fit, mask, &sc->cut, n, m, cd, base + L.inner, s);                         // :216
+    int rc = crowding_sort_known(fit, mask, &sc->cut, n, m, cd, base + L.inner, s);                     // :216
     if (rc) return rc;
     k_sel_keys<<<gn, T, 0, s>>>(rank, cd, n, L.nb, sc, kA, vA);
     EVX_LAUNCH_CHECK();
     size_t tb = L.tmp_bytes;
     EVX_CUDA(cub::DeviceRadixSort::SortPairs(base + L.tmp, tb, kA, kB, vA, vB, (int)n, 0, 2 * L.nb, s));   // :218
-    const int64_t elems = topk * (int64_t)(d + m);
+    const int64_t elems = topk * (int64_t)((out_pop ? d : 0) + m);
     k_sel_gather<<<(unsigned)ceil_div(elems, T), T, 0, s>>>(vB, topk, pop, out_pop ? d : 0, fit_out_src ? fit_out_src : fit,
                                                            m, out_pop, out_fit, out_index);            // :219-222
     EVX_LAUNCH_CHECK();
     return EVX_OK;
+}
+
+static int select_check(const char* who, const float* pop, const float* fit, int64_t n, int32_t d, int32_t m, int64_t topk,
+                        const float* out_pop, const float* out_fit, const int32_t* out_index, void* ws, size_t ws_bytes) {
+    EVX_REQUIRE(n >= 1 && m >= 1 && m <= EVX_MAX_OBJECTIVES && d >= 0, EVX_ERR_ARG, "%s: bad shape n=%lld d=%d m=%d", who,
+                (long long)n, d, m);
+    EVX_REQUIRE(topk >= 1 && topk <= n, EVX_ERR_ARG, "%s: topk=%lld must be in [1, n=%lld]", who, (long long)topk,
+                (long long)n);
+    EVX_REQUIRE(fit && (out_pop == nullptr || (pop && d > 0)) && (out_pop || out_fit || out_index), EVX_ERR_ARG,
+                "%s: null pointer", who);
+    const size_t need = evx_non_dominate_workspace_bytes(n, m);
+    EVX_REQUIRE(need != 0, EVX_ERR_ARG, "%s: n=%lld too large", who, (long long)n);
+    EVX_REQUIRE(ws && ws_bytes >= need, EVX_ERR_WORKSPACE, "%s: workspace %zu < required %zu", who, ws_bytes, need);
+    return EVX_OK;
+}
+
+extern "C" int evx_non_dominate_f32(const float* pop, const float* fit, const float* fit_out_src, int64_t n, int32_t d,
+                                    int32_t m, int64_t topk, float* out_pop, float* out_fit, int32_t* out_index,
+                                    void* ws, size_t ws_bytes, void* stream) {
+    int rc = select_check("evx_non_dominate_f32", pop, fit, n, d, m, topk, out_pop, out_fit, out_index, ws, ws_bytes);
+    if (rc) return rc;
+    char* base = reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(ws), 256));
+    const SelLayout L = sel_layout(n, m);
+    int* rank = reinterpret_cast<int*>(base + L.rank);
+    rc = evx_nds_f32(fit, n, m, rank, base + L.inner, L.inner_bytes, stream);                           // :211
+    if (rc) return rc;
+    return select_by_rank(pop, fit, fit_out_src, rank, n, d, m, topk, out_pop, out_fit, out_index, base, L,
+                          (cudaStream_t)stream);
+}
+
+extern "C" int evx_select_by_rank_f32(const float* pop, const float* fit, const float* fit_out_src, const int32_t* rank,
+                                      int64_t n, int32_t d, int32_t m, int64_t topk, float* out_pop, float* out_fit,
+                                      int32_t* out_index, void* ws, size_t ws_bytes, void* stream) {
+    int rc = select_check("evx_select_by_rank_f32", pop, fit, n, d, m, topk, out_pop, out_fit, out_index, ws, ws_bytes);
+    if (rc) return rc;
+    EVX_REQUIRE(rank, EVX_ERR_ARG, "evx_select_by_rank_f32: null rank");
+    char* base = reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(ws), 256));
+    return select_by_rank(pop, fit, fit_out_src, rank, n, d, m, topk, out_pop, out_fit, out_index, base, sel_layout(n, m),
+                          (cudaStream_t)stream);
 }

@@ -152,18 +152,62 @@ class FusedShardedNonDominatedSort:
         return self.out
 
 
-def sharded_evaluate(problem, state, X_local, group=None):
-    """Evaluate this rank's slice of the population and all-gather the fitness, as
-    std_workflow.py:187-200 + core/distributed.py:49-56 do."""
-    F_local, state = problem.evaluate(state, X_local)
+def sharded_evaluate(problem, state, X, group=None):
+    """Evaluate this rank's slice of the (replicated) candidate matrix and all-gather the fitness, as
+    std_workflow.py:187-200 (slice by process index) + core/distributed.py:49-56 (all_gather) do.
+    Rows are dealt in equal slices; a population that does not divide pads the last slice."""
     if not dist.is_initialized() or dist.get_world_size(group) == 1:
-        return F_local, state
-    world = dist.get_world_size(group)
-    F = torch.empty((F_local.shape[0] * world, F_local.shape[1]), dtype=F_local.dtype, device=F_local.device)
+        return problem.evaluate(state, X)
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    n = X.shape[0]
+    per = -(-n // world)
+    lo = min(rank * per, n)
+    Xl = X[lo:min(lo + per, n)]
+    if Xl.shape[0] < per:                                   # ragged tail: evaluate copies of a valid row, cut off below
+        Xl = torch.cat([Xl, X[:1].expand(per - Xl.shape[0], -1)], dim=0)
+    F_local, state = problem.evaluate(state, Xl.contiguous())
+    F = torch.empty((per * world, F_local.shape[1]), dtype=F_local.dtype, device=F_local.device)
     dist.all_gather_into_tensor(F, F_local.contiguous(), group=group)
-    return F, state
+    return F[:n], state
 
 
 def non_dominated_sort_sharded(x, group=None):
     x = as_f32_cuda(x, "x")
     return ShardedNonDominatedSort(x.shape[0], x.shape[1], group)(x)
+
+
+class ShardedNSGA2:
+    """NSGA-II generation over several GPUs, one process each (BASELINE.json configs[2]).  The state is
+    replicated, as in the reference's multi-device workflow (std_workflow.py:160,187-200): every rank
+    runs the same variation kernel on the same (seed, generation), evaluates ITS slice of the
+    candidates, all-gathers the fitness; then the merged population is ranked by the sharded
+    non-dominated sort (bit matrix split by column panels, fused front exchange) and every rank applies
+    the same survivor selection to the ranks.  Results are identical to the single-GPU NSGA2."""
+
+    def __init__(self, algorithm, group=None, exchange="fused"):
+        self.alg = algorithm
+        self.group = group
+        n, m = 2 * algorithm.pop_size, algorithm.n_objs
+        self.sorter = (FusedShardedNonDominatedSort if exchange == "fused" else ShardedNonDominatedSort)(n, m, group)
+
+    def setup(self, seed=0):
+        return self.alg.setup(seed)
+
+    def step(self, problem, state, pstate=None):
+        from .operators.selection.non_dominate import select_by_rank
+        alg = self.alg
+        if state.generation == 0:                            # init_ask / init_tell once (std_workflow.py:204-214)
+            fit, pstate = sharded_evaluate(problem, pstate, state.population, self.group)
+            state = alg.init_tell(state, fit)
+        cand, state = alg.ask(state)
+        fit, pstate = sharded_evaluate(problem, pstate, cand, self.group)
+        merged_pop = torch.cat([state.population, state.next_generation], dim=0)
+        merged_fit = torch.cat([state.fitness, fit], dim=0)
+        rank = self.sorter(merged_fit)
+        pop, f = select_by_rank(merged_pop, merged_fit, rank, alg.pop_size)
+        return state.replace(population=pop, fitness=f), pstate
+
+    def run(self, problem, state, generations, pstate=None):
+        for _ in range(generations):
+            state, pstate = self.step(problem, state, pstate)
+        return state, pstate

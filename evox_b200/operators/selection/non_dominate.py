@@ -115,7 +115,13 @@ def non_dominate(population, fitness, topk, deduplicate):
         pop, fit = pop[uidx], fit[uidx]
         fit_bak = fit.contiguous()
         fit = torch.where((ar < count)[:, None], fit, torch.full_like(fit, float("inf"))).contiguous()
-    m = fit.shape[1]
+    return _select(pop, fit, fit_bak, topk)
+
+
+def _select(pop, fit, fit_bak, topk, rank=None):
+    """One library call: evx_non_dominate_f32 (sorts, then selects), or evx_select_by_rank_f32 when the
+    caller already holds the ranks (the sharded driver: ranks come from the multi-GPU sort)."""
+    n, m = fit.shape
     pop2 = pop.reshape(n, -1)
     fused_pop = pop2.dtype == torch.float32 and pop2.shape[1] > 0
     pop2 = pop2.contiguous() if fused_pop else pop2
@@ -128,13 +134,25 @@ def non_dominate(population, fitness, topk, deduplicate):
     if nbytes == 0:
         raise ValueError(f"non_dominate: unsupported shape n={n}, m={m}")
     ws = workspace(nbytes, "sel")
-    check(L.evx_non_dominate_f32(pop2.data_ptr() if fused_pop else None, fit.data_ptr(),
-                                 None if fit_bak is None else fit_bak.data_ptr(), n, d, m, topk,
-                                 None if out_pop is None else out_pop.data_ptr(), out_fit.data_ptr(),
-                                 None if out_idx is None else out_idx.data_ptr(), ws.data_ptr(), ws.numel(), stream_ptr()))
+    common = (n, d, m, topk, None if out_pop is None else out_pop.data_ptr(), out_fit.data_ptr(),
+              None if out_idx is None else out_idx.data_ptr(), ws.data_ptr(), ws.numel(), stream_ptr())
+    head = (pop2.data_ptr() if fused_pop else None, fit.data_ptr(), None if fit_bak is None else fit_bak.data_ptr())
+    if rank is None:
+        check(L.evx_non_dominate_f32(*head, *common))
+    else:
+        check(L.evx_select_by_rank_f32(*head, rank.data_ptr(), *common))
     if fused_pop:
         return out_pop.reshape((topk,) + tuple(pop.shape[1:])), out_fit
     return pop[out_idx.long()], out_fit                                  # non-float32 populations: gather by index
+
+
+def select_by_rank(population, fitness, rank, topk):
+    """non_dominate.py:213-222 on ranks computed elsewhere (no counterpart in the reference, whose
+    selection is replicated on every device): used by evox_b200.distributed after the sharded sort."""
+    pop = population.to("cuda")
+    fit = as_f32_cuda(fitness, "fitness")
+    rank = rank.to(device="cuda", dtype=torch.int32).contiguous()
+    return _select(pop, fit, None, int(topk), rank)
 
 
 class NonDominate:

@@ -119,6 +119,12 @@ int evx_non_dominate_f32(const float* pop, const float* fit, const float* fit_ou
                          int32_t m, int64_t topk, float* out_pop, float* out_fit, int32_t* out_index,
                          void* ws, size_t ws_bytes, void* stream);
 
+/* The same selection on ranks the caller already holds (device int32 [n], values in [0, n)): what the
+ * sharded driver uses after the multi-GPU sort has produced the ranks (non_dominate.py:213-222).     */
+int evx_select_by_rank_f32(const float* pop, const float* fit, const float* fit_out_src, const int32_t* rank,
+                           int64_t n, int32_t d, int32_t m, int64_t topk, float* out_pop, float* out_fit,
+                           int32_t* out_index, void* ws, size_t ws_bytes, void* stream);
+
 /* ---- (a7) DTLZ1..7 evaluate -------------------------------------------------------------------
  * replaces problems/numerical/dtlz.py:48-69, 84-103, 115-145, 152-172, 188-208, 244-265, 303-322
  * `DTLZk.evaluate(state, X)`.  X: device float32 [n, d]; F: device float32 [n, m].  Asynchronous. */
@@ -199,11 +205,6 @@ int evx_profile_last(float* prep_ms, float* tiles_ms, float* peel_ms);
  * and its last CTA (out16[4..7]); out16[8..15] are zero.  p == NULL: the values of this host thread's
  * last evx_nds_f32 call made with evx_profile_enable(1).                                            */
 int evx_debug_peel_times(evx_nds_shard* p, uint64_t* out16);
-/* register-only issue-rate probe: runs `iters` dependent-free compare+logic steps per thread on
- * the whole chip and returns the measured pair-tests per second for the inner step the dominance
- * tile kernel uses (the denominator of the compare roofline).  Synchronises.                      */
-int evx_probe_compare_rate(int32_t m, int64_t iters, double* pairs_per_s, void* stream);
-
 #ifdef __cplusplus
 }
 #endif

@@ -52,6 +52,21 @@ for rep in range(2):
     if rank == 0:
         print(f"n={n} m=3 world={world} rep={rep} sampled exactness {good} fronts {f.num_fronts}", flush=True)
     ok &= good
+# NSGA-II generations (configs[2] algorithm, smaller population): evaluation sharded by rows + all-gather,
+# sort sharded by column panels, selection on the gathered ranks - survivors must be bit-identical to the
+# single-GPU generation loop run on this rank's own GPU.
+import evox_b200 as E  # noqa: E402
+from evox_b200.algorithms import NSGA2, run_generations  # noqa: E402
+from evox_b200.distributed import ShardedNSGA2  # noqa: E402
+for pop in (20000, 10001):                                 # the second does not divide by the world size
+    alg = NSGA2(torch.zeros(12), torch.ones(12), n_objs=3, pop_size=pop)
+    prob = E.problems.numerical.DTLZ2(d=12, m=3)
+    s1, _ = run_generations(alg, prob, alg.setup(seed=5), 4)
+    sN, _ = ShardedNSGA2(alg).run(prob, alg.setup(seed=5), 4)
+    good = bool(torch.equal(s1.population, sN.population)) and bool(torch.equal(s1.fitness, sN.fitness))
+    if rank == 0:
+        print(f"NSGA-II pop={pop} world={world}: 4 sharded generations == 4 single-GPU generations {good}", flush=True)
+    ok &= good
 flag = torch.tensor([0 if ok else 1], device="cuda")
 dist.all_reduce(flag)
 print(rank, "ALL OK" if int(flag) == 0 else "MISMATCH", flush=True)
