@@ -51,6 +51,16 @@ constexpr int PW = TW / 32;         // words per panel row (128 B)
 // sign-bit compares serves two rows (N = 100k, M = 10: 1.64 vs 1.78 ms).  A warp always covers 128 rows.
 __host__ __device__ constexpr int tile_rb(int m) { return m <= 3 ? 1 : 2; }
 constexpr int TILE_WARPS = 8;
+// f2 rank table of a panel: entry [g][w] = how many of the panel's g smallest-f2 columns lie in word w
+// (one byte, 0..32), g = 0..TW.  See k_panel_tables.
+constexpr int F2TAB_BYTES = (TW + 1) * PW;
+// Per-panel table blob used by the M = 3 tile kernel (k_panel_tables), byte offsets:
+constexpr int PT_SF2 = 0;                                  // float [TW]      the panel's f2 values, ascending
+constexpr int PT_S1 = PT_SF2 + 4 * TW;                     // float [PW][32]  per word: its columns' f1 values, ascending
+constexpr int PT_TAB = PT_S1 + 4 * TW;                     // uint8 [TW+1][PW] f2 rank -> columns of word w below that rank
+constexpr int PT_M1 = PT_TAB + F2TAB_BYTES;                // uint32 [PW][33] per word: columns whose f1 rank is >= k
+constexpr int PT_BYTES = PT_M1 + 4 * PW * 33;
+static_assert(PT_BYTES % 16 == 0 && PT_TAB % 16 == 0, "table blob is copied in 16-byte pieces");
 constexpr int TILE_ROWS_PER_WARP = 128;                 // slabs per warp = 128 / (32 * rows per lane)
 constexpr int APPLY_WARPS = 8;
 constexpr int SMALL_PATH_MAX_N = 1024;   // populations of at most one panel take the direct small path
@@ -73,7 +83,7 @@ struct Layout {
     int64_t n, npad;
     int m, world, rank, np, npl, npl_max;
     size_t keys, idxA, idxB, skeyA, skeyB, flags, incl, cubtmp, cubtmp_bytes, ucols, row2u, count,
-        rank_u, flist, flist2, cplanes, mask, scal, bits, total, tcols, bkeyA, bkeyB, label, partials, pdone, pcnt;
+        rank_u, flist, flist2, cplanes, mask, scal, bits, total, tcols, bkeyA, bkeyB, label, partials, pdone, pcnt, ptab;
     int kplanes;
     int64_t bits_words;
 };
@@ -135,6 +145,7 @@ static Layout make_layout(int64_t n, int m, int world, int rank) {
     L.bkeyA = take(sizeof(uint64_t) * n);
     L.bkeyB = take(sizeof(uint64_t) * n);
     L.label = take(sizeof(int) * n);
+    L.ptab = take(m == 3 ? (size_t)PT_BYTES * (size_t)L.np : 0);              // per-panel tables of the M = 3 tile kernel
     L.row2u = take(sizeof(int) * n);
     L.count = take(sizeof(int) * (size_t)L.npl_max * TW);
     L.rank_u = take(sizeof(int) * (size_t)L.npl_max * TW);
@@ -256,6 +267,82 @@ __global__ void k_relabel_rows(int* __restrict__ row2u, const int* __restrict__ 
 }
 
 // ------------------------------------------------------------------------------------------------
+// stage 1c: per-panel tables (M = 3)
+// ------------------------------------------------------------------------------------------------
+// f2: for a row r and a word w of panel J (32 columns, ascending f2), the columns with f2_r <= f2_c form
+// a suffix of the word; its start is the number of the word's columns with f2_c < f2_r.  Instead of one
+// 5-step binary search per (row, word) - 32 per row and panel - the row is searched ONCE in the panel's
+// 1024 f2 values (sf2, ascending): g = #{c in panel : f2_c < f2_r}, and tab[g][w] says how many of those
+// g columns belong to word w.  (g always falls on a boundary between distinct values, so ties in the
+// sorted order do not matter.)
+// f1: the words of a panel are consecutive runs of the block's f1 order, so for a row only ONE word
+// needs an f1 test per column; for it the word's f1 values are kept sorted (s1) with, for every rank k,
+// the mask m1[w][k] of the word's columns whose f1 rank is >= k: a 5-step search and one load.
+// One CTA per panel: bitonic sort of (f2 key, column) in shared memory, warp w walks the sorted order
+// and counts its own word's columns; warp w also ranks its word's 32 f1 values.
+__global__ void __launch_bounds__(TW)
+k_panel_tables(const float* __restrict__ ucols, int64_t npad, const Scal* __restrict__ scal, uint8_t* __restrict__ ptab) {
+    __shared__ unsigned long long key[TW];
+    __shared__ uint8_t wordof[TW];
+    __shared__ __align__(16) uint8_t tab[F2TAB_BYTES];
+    const int J = blockIdx.x, t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int U = scal->U;
+    const int c = J * TW + t;
+    const float* f1 = ucols + npad;
+    const float* f2 = ucols + 2 * npad;
+    uint8_t* blob = ptab + (size_t)J * PT_BYTES;
+    // ---- f1: rank of my column inside my word (ties by column), sorted values and masks ----
+    {
+        const float v = (c < U) ? f1[c] : __int_as_float(0x7FC00000);
+        const uint32_t k1 = (c < U) ? float_key(v) : 0xFFFFFFFFu;
+        int rk = 0;
+#pragma unroll
+        for (int b = 0; b < 32; ++b) {
+            const uint32_t o = __shfl_sync(0xFFFFFFFFu, k1, b);
+            rk += (o < k1) || (o == k1 && b < lane);
+        }
+        reinterpret_cast<float*>(blob + PT_S1)[warp * 32 + rk] = v;         // NaN for missing columns: never "< r"
+        uint32_t* m1 = reinterpret_cast<uint32_t*>(blob + PT_M1) + warp * 33;
+        for (int k = 0; k <= 32; ++k) {
+            const uint32_t mk = __ballot_sync(0xFFFFFFFFu, rk >= k);
+            if (lane == 0) m1[k] = mk;
+        }
+    }
+    // ---- f2 ----
+    key[t] = (c < U) ? (((unsigned long long)float_key(f2[c]) << 32) | (unsigned int)t) : ~0ull;
+    __syncthreads();
+    for (int k = 2; k <= TW; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const int o = t ^ j;
+            if (o > t) {
+                const unsigned long long a = key[t], b = key[o];
+                const bool up = (t & k) == 0;
+                if ((a > b) == up) { key[t] = b; key[o] = a; }
+            }
+            __syncthreads();
+        }
+    }
+    const unsigned long long kk = key[t];
+    const bool valid = kk != ~0ull;
+    const int col = (int)(unsigned int)kk;                                  // column within the panel
+    reinterpret_cast<float*>(blob + PT_SF2)[t] = valid ? f2[J * TW + col] : __int_as_float(0x7FC00000);   // NaN: never "< r"
+    wordof[t] = valid ? (uint8_t)(col >> 5) : (uint8_t)255;
+    __syncthreads();
+    int base = 0;                                                           // warp <-> word
+    if (lane == 0) tab[warp] = 0;                                           // g = 0
+    for (int ch = 0; ch < TW / 32; ++ch) {
+        const int p = ch * 32 + lane;
+        const uint32_t b = __ballot_sync(0xFFFFFFFFu, wordof[p] == warp);
+        tab[(p + 1) * PW + warp] = (uint8_t)(base + __popc(b & (0xFFFFFFFFu >> (31 - lane))));
+        base += __popc(b);
+    }
+    __syncthreads();
+    uint4* dst = reinterpret_cast<uint4*>(blob + PT_TAB);
+    const uint4* src = reinterpret_cast<const uint4*>(tab);
+    for (int i = t; i < F2TAB_BYTES / 16; i += TW) dst[i] = src[i];
+}
+
+// ------------------------------------------------------------------------------------------------
 // stage 2: dominance tiles
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void csa(uint32_t& hi, uint32_t& lo, uint32_t a, uint32_t b, uint32_t c) {
@@ -339,6 +426,21 @@ __device__ __forceinline__ void word_fail(const float* f1w, const float* restw, 
     }
 }
 
+// g = #{c : sf2[c] < r} over a panel's TW ascending f2 values in shared memory (NaN padding at the end
+// never compares below): ten steps of a byte-address walk (load, compare, predicated add).
+__device__ __forceinline__ int panel_rank(uint32_t saddr, const float* sf2s, float r) {
+    uint32_t a = saddr;
+#pragma unroll
+    for (int step = TW / 2; step >= 1; step >>= 1) {
+        float v;
+        asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a + 4u * (uint32_t)(step - 1)));
+        if (v < r) a += 4u * (uint32_t)step;
+    }
+    int g = (int)((a - saddr) >> 2);                   // 0 .. TW-1
+    if (g == TW - 1 && sf2s[TW - 1] < r) g = TW;
+    return g;
+}
+
 // Columns of a word are in ascending f2: the pairs with f2_row <= f2_col form a suffix of the word.
 // Lower bound among the first 31 columns by walking a shared-memory BYTE address (load, compare,
 // predicated add: three instructions per step - the compiler's version kept an element index and
@@ -363,7 +465,7 @@ __device__ __forceinline__ uint32_t f2_mask(uint32_t caddr, float c15, float c31
     return (c31 < r) ? 0u : __funnelshift_l(0u, 0xFFFFFFFFu, a >> 2);
 }
 
-constexpr int TILE_NUP = 5;                            // count planes 8 .. 128 (a warp's 128 rows)
+constexpr int TILE_NUP = 6;                            // count planes 8 .. 256 (a warp's rows: 128, or 256 for M = 3)
 
 struct CountPlanes {
     uint32_t ones = 0, twos = 0, fours = 0, up[TILE_NUP] = {};
@@ -403,7 +505,7 @@ __device__ __forceinline__ void slab_out(const uint32_t* sl, uint32_t* gout, int
 // (three rounds, a plane more each round), and only the sum is turned into integers - one global
 // atomic per non-zero column.  `pl` is scratch of TILE_WARPS * FLUSH_PLANES * 32 words that no warp
 // uses any more (the caller has synchronised).
-constexpr int FLUSH_PLANES = 3 + TILE_NUP + 3;         // 8 warps x 128 rows: counts up to 1024
+constexpr int FLUSH_PLANES = 3 + TILE_NUP + 3;         // 8 warps x 256 rows: counts up to 2048
 __device__ __forceinline__ void counts_flush(const CountPlanes& cp, int lane, int warp, uint32_t* pl,
                                              int* __restrict__ count, int l) {
     uint32_t* mine = pl + warp * FLUSH_PLANES * 32 + lane;
@@ -581,6 +683,105 @@ __device__ __forceinline__ void tile_offdiag(const float* __restrict__ ucols, in
     counts_flush(cp, lane, warp, stage, count, l);
 }
 
+// ---- off-diagonal CTA, M = 3: lane <-> word, no transposition --------------------------------------
+// The panel's columns are ordered by f1 at word granularity (word w holds the w-th run of 32 columns of
+// the block's f1 order) and by f2 inside a word.  For a row r of a lower block (f0 decided by the
+// order) that leaves, per word:
+//   words entirely below r in f1            -> no pair passes              (w < ws_r)
+//   the ONE word whose f1 range contains r  -> mask m1[ws_r][k_r]          (k_r = rank of f1_r in that word)
+//   words entirely at or above r in f1      -> f1 passes for every pair    (w > ws_r)
+// and f2_r <= f2_c is a suffix of the word whose start is a table byte: tab[g_r][w], g_r = rank of f2_r
+// among the panel's f2 values (k_panel_tables).  So a slab of 32 rows takes one pass with lane <-> row
+// (g_r by a 10-step search, ws_r by a 5-step search over the words' smallest f1, k_r by a 5-step search
+// in word ws_r's sorted f1 values), which leaves one 16-byte record per row in shared memory, and then
+// one pass with lane <-> WORD over the 32 rows: the record arrives by one broadcast load, the lane reads
+// ONE table byte, shifts, masks, stores its word of row r (the warp stores the row's full 128-byte
+// line) and feeds it to the carry-save column counters - no shared-memory staging of results at all.
+__device__ __forceinline__ void tile_offdiag_m3(const uint8_t* __restrict__ ptab, const float* __restrict__ ucols,
+                                                int64_t npad, int U, int l, int col0, int row0, int rowlimit, int slabs,
+                                                uint32_t* __restrict__ bits, int* __restrict__ count, int world, int rank,
+                                                uint32_t* smem) {
+    unsigned char* sb = reinterpret_cast<unsigned char*>(smem);
+    const float* f2s = reinterpret_cast<const float*>(sb + PT_SF2);        // [TW]
+    const float* s1 = reinterpret_cast<const float*>(sb + PT_S1);          // [PW][32]
+    const uint32_t* m1 = reinterpret_cast<const uint32_t*>(sb + PT_M1);    // [PW][33]
+    uint32_t* wcm = reinterpret_cast<uint32_t*>(sb + PT_BYTES);            // [PW] valid-column mask of each word
+    uint4* rec = reinterpret_cast<uint4*>(sb + PT_BYTES + 4 * PW);         // [TILE_WARPS][32] per-row records
+    uint32_t* flush = smem;                                                // counts_flush scratch: reuses the (then dead) tables
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(ptab + (size_t)(col0 / TW) * PT_BYTES);
+        uint4* dst = reinterpret_cast<uint4*>(sb);
+        for (int t = threadIdx.x; t < PT_BYTES / 16; t += blockDim.x) dst[t] = src[t];
+    }
+    if (threadIdx.x < PW) {
+        const int ncol = min(32, U - (col0 + (int)threadIdx.x * 32));      // valid columns in this word
+        wcm[threadIdx.x] = (ncol >= 32) ? 0xFFFFFFFFu : (ncol <= 0 ? 0u : ((1u << ncol) - 1u));
+    }
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t f2addr = (uint32_t)__cvta_generic_to_shared(f2s);
+    const uint32_t tabaddr = (uint32_t)__cvta_generic_to_shared(sb + PT_TAB);
+    const uint32_t mywcm = wcm[lane];
+    uint4* myrec = rec + warp * 32;
+    const uint32_t recaddr = (uint32_t)__cvta_generic_to_shared(myrec);
+    CountPlanes cp;
+
+    for (int sidx = 0; sidx < slabs; ++sidx) {
+        const int rs = row0 + (sidx * TILE_WARPS + warp) * 32;              // first row of this slab
+        if (rs >= rowlimit) break;                                          // warp-uniform
+        // ---- lane <-> row ----
+        const float xf1 = ucols[npad + rs + lane], xf2 = ucols[2 * npad + rs + lane];   // rows of a lower block: all valid
+        const int g = panel_rank(f2addr, f2s, xf2);
+        int ws = 0;                                                         // last word whose smallest f1 is < xf1 (0 if none)
+#pragma unroll
+        for (int step = PW / 2; step >= 1; step >>= 1)
+            if (s1[(ws + step) * 32] < xf1) ws += step;                     // (NaN = word without columns: never)
+        // words below ws: every f1 < xf1 (word ranges ascend); words above: every f1 >= xf1; word ws: by rank
+        const float* sw = s1 + ws * 32;
+        int k = 0;                                                          // columns of word ws with f1 < xf1
+#pragma unroll
+        for (int step = 16; step >= 1; step >>= 1)
+            if (sw[k + step - 1] < xf1) k += step;
+        if (k == 31 && sw[31] < xf1) k = 32;
+        __syncwarp();                                                       // the previous slab's records have been read
+        myrec[lane] = make_uint4(tabaddr + (uint32_t)g * PW, (uint32_t)ws, m1[ws * 33 + k], 0u);
+        __syncwarp();
+        // ---- lane <-> word ----
+        uint32_t* gout = bits + bits_offset(l, rs, world, rank) + lane;
+#pragma unroll 1
+        for (int r0 = 0; r0 < 32; r0 += 8) {
+            uint32_t v[8];
+#pragma unroll
+            for (int t = 0; t < 8; ++t) {
+                uint32_t ra, rw, rm, rz;
+                asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(ra), "=r"(rw), "=r"(rm), "=r"(rz)
+                             : "r"(recaddr + 16u * (uint32_t)(r0 + t)));
+                uint32_t cnt;                                               // columns of my word with f2 < the row's
+                asm volatile("ld.shared.u8 %0, [%1];" : "=r"(cnt) : "r"(ra + (uint32_t)lane));
+                uint32_t mk;
+                asm("shf.l.clamp.b32 %0, %1, %2, %3;" : "=r"(mk) : "r"(0u), "r"(0xFFFFFFFFu), "r"(cnt));   // ~0 << cnt, 0 at 32
+                const uint32_t keep = (uint32_t)lane > rw ? mywcm : ((uint32_t)lane == rw ? (mywcm & rm) : 0u);
+                v[t] = mk & keep;
+            }
+#pragma unroll
+            for (int t = 0; t < 8; ++t) gout[(int64_t)(r0 + t) * PW2] = v[t];
+            uint32_t ta, tb, fa, fb, e;
+            csa(ta, cp.ones, cp.ones, v[0], v[1]);
+            csa(tb, cp.ones, cp.ones, v[2], v[3]);
+            csa(fa, cp.twos, cp.twos, ta, tb);
+            csa(ta, cp.ones, cp.ones, v[4], v[5]);
+            csa(tb, cp.ones, cp.ones, v[6], v[7]);
+            csa(fb, cp.twos, cp.twos, ta, tb);
+            csa(e, cp.fours, cp.fours, fa, fb);
+#pragma unroll
+            for (int p = 0; p < TILE_NUP; ++p) { const uint32_t c = cp.up[p] & e; cp.up[p] ^= e; e = c; }
+        }
+    }
+    __syncthreads();
+    counts_flush(cp, lane, warp, flush, count, l);
+}
+
 // ---- diagonal CTA: a block against its own panel ---------------------------------------------------
 // Either direction may dominate inside a block, so all M objectives are tested (FSETP chain) and
 // only i == j is excluded (rows are unique).  1/NP of the work.
@@ -648,8 +849,9 @@ __device__ __forceinline__ void tile_diag(const float* __restrict__ ucols, int64
 // Off-diagonal tiles: grid = (row chunks, owned panels); chunks at or past the panel's own block leave.
 template <int M>
 __global__ void __launch_bounds__(TILE_WARPS * 32)
-k_dominance_tiles(const float* __restrict__ ucols, int64_t npad, const Scal* __restrict__ scal,
-                  uint32_t* __restrict__ bits, int* __restrict__ count, int world, int rank, int slabs) {
+k_dominance_tiles(const float* __restrict__ ucols, const uint8_t* __restrict__ ptab, int64_t npad,
+                  const Scal* __restrict__ scal, uint32_t* __restrict__ bits, int* __restrict__ count, int world, int rank,
+                  int slabs) {
     const int l = blockIdx.y;
     const int J = panel_of_local(l, world, rank);
     const int U = scal->U;
@@ -658,7 +860,8 @@ k_dominance_tiles(const float* __restrict__ ucols, int64_t npad, const Scal* __r
     const int row0 = blockIdx.x * (slabs * TILE_WARPS * 32 * tile_rb(M));
     if (row0 >= col0) return;
     extern __shared__ __align__(128) uint32_t smem[];
-    tile_offdiag<M>(ucols, npad, U, l, col0, row0, col0, slabs, bits, count, world, rank, smem);
+    if constexpr (M == 3) tile_offdiag_m3(ptab, ucols, npad, U, l, col0, row0, col0, slabs, bits, count, world, rank, smem);
+    else tile_offdiag<M>(ucols, npad, U, l, col0, row0, col0, slabs, bits, count, world, rank, smem);
 }
 
 // Diagonal tiles: grid = (row chunks of one block, owned panels).
@@ -1616,7 +1819,8 @@ static int launch_tiles(const Plan& P, cudaStream_t s) {
     constexpr int SLAB = 32 * tile_rb(M), MAX_SLABS = TILE_ROWS_PER_WARP / SLAB;
     static_assert(TW % (MAX_SLABS * TILE_WARPS * SLAB) == 0, "a CTA's rows must tile a block");
     const size_t stage_words = (size_t)TILE_WARPS * PW * (SLAB + 1);
-    const size_t smem = sizeof(uint32_t) * ((size_t)(M > 1 ? M - 1 : 1) * TW + stage_words + 3 * PW);
+    const size_t smem = (M == 3) ? (size_t)PT_BYTES + 4 * PW + 16 * 32 * TILE_WARPS
+                                 : sizeof(uint32_t) * ((size_t)(M > 1 ? M - 1 : 1) * TW + stage_words + 3 * PW);
     const size_t smem_diag = sizeof(uint32_t) * ((size_t)M * TW + stage_words + TW);
     EVX_CUDA(cudaFuncSetAttribute(k_dominance_tiles<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     EVX_CUDA(cudaFuncSetAttribute(k_dominance_diag<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_diag));
@@ -1624,11 +1828,13 @@ static int launch_tiles(const Plan& P, cudaStream_t s) {
     // warp as still leave a few waves of CTAs on the chip
     int slabs = MAX_SLABS;
     while (slabs > 1 && (int64_t)L.npl * L.np * (TW / (slabs * TILE_WARPS * SLAB)) / 2 < 148 * 5 * 4) slabs >>= 1;
-    dim3 grid((unsigned)ceil_div(L.npad, slabs * TILE_WARPS * SLAB), (unsigned)L.npl);
+    // M = 3: a CTA stages 45 KB of panel tables, so it takes twice the rows when there are CTAs to spare
+    const int slabs_off = (M == 3 && slabs == MAX_SLABS && (int64_t)L.npl * L.np / 4 >= 148 * 4 * 8) ? 2 * MAX_SLABS : slabs;
+    dim3 grid((unsigned)ceil_div(L.npad, slabs_off * TILE_WARPS * SLAB), (unsigned)L.npl);
     if (L.np > 1) {
-        k_dominance_tiles<M><<<grid, TILE_WARPS * 32, smem, s>>>(P.at<float>(L.ucols), L.npad, P.at<Scal>(L.scal),
-                                                                  P.at<uint32_t>(L.bits), P.at<int>(L.count), L.world,
-                                                                  L.rank, slabs);
+        k_dominance_tiles<M><<<grid, TILE_WARPS * 32, smem, s>>>(P.at<float>(L.ucols), P.at<uint8_t>(L.ptab), L.npad,
+                                                                  P.at<Scal>(L.scal), P.at<uint32_t>(L.bits),
+                                                                  P.at<int>(L.count), L.world, L.rank, slabs_off);
         EVX_LAUNCH_CHECK();
     }
     dim3 gdiag((unsigned)ceil_div(TW, slabs * TILE_WARPS * SLAB), (unsigned)L.npl);
@@ -1697,6 +1903,10 @@ static int build(const Plan& P, const float* x, cudaStream_t s, cudaEvent_t tile
     }
 
     if (L.npl == 0) return EVX_OK;
+    if (m == 3 && L.np > 1) {                          // f2 rank tables of the panels (used by the off-diagonal tiles)
+        k_panel_tables<<<(unsigned)L.np, TW, 0, s>>>(P.at<float>(L.ucols), L.npad, scal, P.at<uint8_t>(L.ptab));
+        EVX_LAUNCH_CHECK();
+    }
     int rc = EVX_OK;
     if (tiles_begin) EVX_CUDA(cudaEventRecord(tiles_begin, s));
     switch (m) {
