@@ -704,14 +704,15 @@ __device__ __forceinline__ void tile_offdiag_m3(const uint8_t* __restrict__ ptab
     unsigned char* sb = reinterpret_cast<unsigned char*>(smem);
     const float* f2s = reinterpret_cast<const float*>(sb + PT_SF2);        // [TW]
     const float* s1 = reinterpret_cast<const float*>(sb + PT_S1);          // [PW][32]
-    const uint32_t* m1 = reinterpret_cast<const uint32_t*>(sb + PT_M1);    // [PW][33]
-    uint32_t* wcm = reinterpret_cast<uint32_t*>(sb + PT_BYTES);            // [PW] valid-column mask of each word
-    uint4* rec = reinterpret_cast<uint4*>(sb + PT_BYTES + 4 * PW);         // [TILE_WARPS][32] per-row records
+    // the f1 rank masks are read once per row: they stay in global memory (L1) so that five CTAs fit on an SM
+    const uint32_t* m1 = reinterpret_cast<const uint32_t*>(ptab + (size_t)(col0 / TW) * PT_BYTES + PT_M1);   // [PW][33]
+    uint32_t* wcm = reinterpret_cast<uint32_t*>(sb + PT_M1);               // [PW] valid-column mask of each word
+    uint2* rec = reinterpret_cast<uint2*>(sb + PT_M1 + 4 * PW);            // [TILE_WARPS][32] per-row records
     uint32_t* flush = smem;                                                // counts_flush scratch: reuses the (then dead) tables
     {
         const uint4* src = reinterpret_cast<const uint4*>(ptab + (size_t)(col0 / TW) * PT_BYTES);
         uint4* dst = reinterpret_cast<uint4*>(sb);
-        for (int t = threadIdx.x; t < PT_BYTES / 16; t += blockDim.x) dst[t] = src[t];
+        for (int t = threadIdx.x; t < PT_M1 / 16; t += blockDim.x) dst[t] = src[t];
     }
     if (threadIdx.x < PW) {
         const int ncol = min(32, U - (col0 + (int)threadIdx.x * 32));      // valid columns in this word
@@ -723,7 +724,7 @@ __device__ __forceinline__ void tile_offdiag_m3(const uint8_t* __restrict__ ptab
     const uint32_t f2addr = (uint32_t)__cvta_generic_to_shared(f2s);
     const uint32_t tabaddr = (uint32_t)__cvta_generic_to_shared(sb + PT_TAB);
     const uint32_t mywcm = wcm[lane];
-    uint4* myrec = rec + warp * 32;
+    uint2* myrec = rec + warp * 32;
     const uint32_t recaddr = (uint32_t)__cvta_generic_to_shared(myrec);
     CountPlanes cp;
 
@@ -745,7 +746,7 @@ __device__ __forceinline__ void tile_offdiag_m3(const uint8_t* __restrict__ ptab
             if (sw[k + step - 1] < xf1) k += step;
         if (k == 31 && sw[31] < xf1) k = 32;
         __syncwarp();                                                       // the previous slab's records have been read
-        myrec[lane] = make_uint4(tabaddr + (uint32_t)g * PW, (uint32_t)ws, m1[ws * 33 + k], 0u);
+        myrec[lane] = make_uint2(((tabaddr + (uint32_t)g * PW) << 8) | (uint32_t)ws, __ldg(m1 + ws * 33 + k));
         __syncwarp();
         // ---- lane <-> word ----
         uint32_t* gout = bits + bits_offset(l, rs, world, rank) + lane;
@@ -754,11 +755,11 @@ __device__ __forceinline__ void tile_offdiag_m3(const uint8_t* __restrict__ ptab
             uint32_t v[8];
 #pragma unroll
             for (int t = 0; t < 8; ++t) {
-                uint32_t ra, rw, rm, rz;
-                asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(ra), "=r"(rw), "=r"(rm), "=r"(rz)
-                             : "r"(recaddr + 16u * (uint32_t)(r0 + t)));
+                uint32_t rp, rm;                                            // (table row address << 8 | ws_r), m1 mask
+                asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(rp), "=r"(rm) : "r"(recaddr + 8u * (uint32_t)(r0 + t)));
+                const uint32_t rw = rp & 0xFFu;
                 uint32_t cnt;                                               // columns of my word with f2 < the row's
-                asm volatile("ld.shared.u8 %0, [%1];" : "=r"(cnt) : "r"(ra + (uint32_t)lane));
+                asm volatile("ld.shared.u8 %0, [%1];" : "=r"(cnt) : "r"((rp >> 8) + (uint32_t)lane));
                 uint32_t mk;
                 asm("shf.l.clamp.b32 %0, %1, %2, %3;" : "=r"(mk) : "r"(0u), "r"(0xFFFFFFFFu), "r"(cnt));   // ~0 << cnt, 0 at 32
                 const uint32_t keep = (uint32_t)lane > rw ? mywcm : ((uint32_t)lane == rw ? (mywcm & rm) : 0u);
@@ -1819,7 +1820,7 @@ static int launch_tiles(const Plan& P, cudaStream_t s) {
     constexpr int SLAB = 32 * tile_rb(M), MAX_SLABS = TILE_ROWS_PER_WARP / SLAB;
     static_assert(TW % (MAX_SLABS * TILE_WARPS * SLAB) == 0, "a CTA's rows must tile a block");
     const size_t stage_words = (size_t)TILE_WARPS * PW * (SLAB + 1);
-    const size_t smem = (M == 3) ? (size_t)PT_BYTES + 4 * PW + 16 * 32 * TILE_WARPS
+    const size_t smem = (M == 3) ? (size_t)PT_M1 + 4 * PW + 8 * 32 * TILE_WARPS
                                  : sizeof(uint32_t) * ((size_t)(M > 1 ? M - 1 : 1) * TW + stage_words + 3 * PW);
     const size_t smem_diag = sizeof(uint32_t) * ((size_t)M * TW + stage_words + TW);
     EVX_CUDA(cudaFuncSetAttribute(k_dominance_tiles<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
