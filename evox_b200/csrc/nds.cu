@@ -83,7 +83,7 @@ struct Layout {
     int64_t n, npad;
     int m, world, rank, np, npl, npl_max;
     size_t keys, idxA, idxB, skeyA, skeyB, flags, incl, cubtmp, cubtmp_bytes, ucols, row2u, count,
-        rank_u, flist, flist2, cplanes, mask, scal, bits, total, tcols, bkeyA, bkeyB, label, partials, pdone, pcnt, ptab;
+        rank_u, flist, flist2, cplanes, mask, scal, bits, total, tcols, label, partials, pdone, pcnt, ptab;
     int kplanes;
     int64_t bits_words;
 };
@@ -109,14 +109,11 @@ __host__ __device__ __forceinline__ int64_t bits_offset(int l, int64_t row, int 
 }
 
 static size_t cub_temp_bytes(int64_t n) {
-    size_t a = 0, b = 0, c = 0;
-    cub::DeviceRadixSort::SortPairs(nullptr, c, (const uint64_t*)nullptr, (uint64_t*)nullptr,
-                                    (const int*)nullptr, (int*)nullptr, (int)n);
+    size_t a = 0, b = 0;
     cub::DeviceRadixSort::SortPairs(nullptr, a, (const uint32_t*)nullptr, (uint32_t*)nullptr,
                                     (const int*)nullptr, (int*)nullptr, (int)n);
     cub::DeviceScan::InclusiveSum(nullptr, b, (const int*)nullptr, (int*)nullptr, (int)n);
-    a = a > b ? a : b;
-    return a > c ? a : c;
+    return a > b ? a : b;
 }
 
 static Layout make_layout(int64_t n, int m, int world, int rank) {
@@ -142,8 +139,6 @@ static Layout make_layout(int64_t n, int m, int world, int rank) {
     L.cubtmp = take(L.cubtmp_bytes);
     L.ucols = take(sizeof(float) * (size_t)m * L.npad);
     L.tcols = take(sizeof(float) * (size_t)m * L.npad);
-    L.bkeyA = take(sizeof(uint64_t) * n);
-    L.bkeyB = take(sizeof(uint64_t) * n);
     L.label = take(sizeof(int) * n);
     L.ptab = take(m == 3 ? (size_t)PT_BYTES * (size_t)L.np : 0);              // per-panel tables of the M = 3 tile kernel
     L.row2u = take(sizeof(int) * n);
@@ -225,38 +220,52 @@ __global__ void k_scatter_unique(const float* __restrict__ x, const int* __restr
 // they are re-ordered by f1.  Between different blocks the lexicographic order still decides f0
 // (lower block => f0 <=), so off-diagonal tiles test objectives 1..M-1 only; and because both the
 // rows of a warp's slab and the 32 columns of a word are now contiguous in f1, whole (slab, word)
-// sub-tiles are decided by one compare of their f1 ranges: all-fail (skipped) or all-pass on f1
-// (one objective fewer).  Inside a block either direction may dominate: diagonal tiles test all M.
-__global__ void k_block_keys(const float* __restrict__ tcols, int64_t n, int64_t npad, int m, int np,
-                             const Scal* __restrict__ scal, uint64_t* __restrict__ keys, int* __restrict__ vals) {
-    const int64_t u = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (u >= n) return;
-    const bool valid = u < scal->U;
-    const uint32_t f1 = (valid && m > 1) ? float_key(tcols[npad + u]) : 0u;
-    keys[u] = valid ? (((uint64_t)(u / TW) << 32) | f1) : ((uint64_t)np << 32);     // invalid: past every block
-    vals[u] = (int)u;
-}
-
-// Second level: inside a block, every run of 32 consecutive (f1-ordered) positions - one bit-matrix
-// word - is re-ordered by f2, so that "f2_row <= f2_col" over a word is a suffix mask found by a
-// 5-step binary search instead of 32 compares.
-__global__ void k_word_keys(const float* __restrict__ tcols, const int* __restrict__ perm1, int64_t n, int64_t npad,
-                            int np, const Scal* __restrict__ scal, uint64_t* __restrict__ keys) {
-    const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (v >= n) return;
-    const bool valid = v < scal->U;
-    keys[v] = valid ? (((uint64_t)(v >> 5) << 32) | float_key(tcols[2 * npad + perm1[v]]))
-                    : ((uint64_t)np * (TW / 32) << 32);
-}
-
-__global__ void k_block_permute(const float* __restrict__ tcols, const int* __restrict__ perm, int64_t n,
-                                int64_t npad, int m, const Scal* __restrict__ scal, float* __restrict__ ucols,
-                                int* __restrict__ label_of_u) {
-    const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (v >= n || v >= scal->U) return;
-    const int u = perm[v];
-    label_of_u[u] = (int)v;
-    for (int k = 0; k < m; ++k) ucols[(int64_t)k * npad + v] = tcols[(int64_t)k * npad + u];
+// sub-tiles are decided by their f1 ranges.  Inside a block either direction may dominate: diagonal
+// tiles test all M.  Second level: inside a block, every run of 32 consecutive (f1-ordered) positions -
+// one bit-matrix word - is re-ordered by f2, so that "f2_row <= f2_col" over a word is a suffix mask.
+// One CTA per block: bitonic sort of (f1 key, position) in shared memory, then warp w ranks the 32 rows
+// of word w by f2 with shuffles; rows are written to their label (ucols) and label_of_u is filled.
+// (Any order with these two properties gives the same ranks; ties are broken by position.)
+__global__ void __launch_bounds__(TW)
+k_block_labels(const float* __restrict__ tcols, int64_t npad, int m, const Scal* __restrict__ scal,
+               float* __restrict__ ucols, int* __restrict__ label_of_u) {
+    __shared__ unsigned long long key[TW];
+    const int b = blockIdx.x, t = threadIdx.x, lane = t & 31;
+    const int U = scal->U;
+    const int64_t base = (int64_t)b * TW;
+    if (base >= U) return;
+    const bool valid = base + t < U;
+    key[t] = valid ? (((unsigned long long)(m > 1 ? float_key(tcols[npad + base + t]) : 0u) << 32) | (unsigned int)t) : ~0ull;
+    __syncthreads();
+    for (int k = 2; k <= TW; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const int o = t ^ j;
+            if (o > t) {
+                const unsigned long long a = key[t], c = key[o];
+                const bool up = (t & k) == 0;
+                if ((a > c) == up) { key[t] = c; key[o] = a; }
+            }
+            __syncthreads();
+        }
+    }
+    const unsigned long long kk = key[t];                                  // position t of the f1 order holds row `src`
+    const bool have = kk != ~0ull;
+    const int src = (int)(unsigned int)kk;
+    int q = t;                                                              // final position inside the block
+    if (m >= 3) {
+        const uint32_t k2 = have ? float_key(tcols[2 * npad + base + src]) : 0xFFFFFFFFu;
+        int rk = 0;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            const uint32_t o = __shfl_sync(0xFFFFFFFFu, k2, i);
+            rk += (o < k2) || (o == k2 && i < lane);
+        }
+        q = (t & ~31) + rk;                                                 // missing rows (largest key) stay at the end
+    }
+    if (have) {
+        label_of_u[base + src] = (int)(base + q);
+        for (int k = 0; k < m; ++k) ucols[(int64_t)k * npad + base + q] = tcols[(int64_t)k * npad + base + src];
+    }
 }
 
 __global__ void k_relabel_rows(int* __restrict__ row2u, const int* __restrict__ label_of_u, int64_t n) {
@@ -1879,29 +1888,12 @@ static int build(const Plan& P, const float* x, cudaStream_t s, cudaEvent_t tile
     k_scatter_unique<<<gn, T, 0, s>>>(x, idx_cur, P.at<int>(L.incl), P.at<int>(L.flags), n, m, L.npad, scal,
                                       P.at<float>(L.tcols), P.at<int>(L.row2u));
     EVX_LAUNCH_CHECK();
-    // block-local f1 order (stable 64-bit radix sort on (block, f1 key)), then gather into place
-    {
-        int bbits = 1;
-        while ((1ll << bbits) < L.np + 1) ++bbits;
-        k_block_keys<<<gn, T, 0, s>>>(P.at<float>(L.tcols), n, L.npad, m, L.np, scal, P.at<uint64_t>(L.bkeyA), idx_cur);
-        EVX_LAUNCH_CHECK();
-        size_t tb2 = L.cubtmp_bytes;
-        EVX_CUDA(cub::DeviceRadixSort::SortPairs(P.at<void>(L.cubtmp), tb2, P.at<uint64_t>(L.bkeyA),
-                                                 P.at<uint64_t>(L.bkeyB), idx_cur, idx_nxt, (int)n, 0, 32 + bbits, s));
-        if (m >= 3) {                                  // word-local f2 order
-            k_word_keys<<<gn, T, 0, s>>>(P.at<float>(L.tcols), idx_nxt, n, L.npad, L.np, scal, P.at<uint64_t>(L.bkeyA));
-            EVX_LAUNCH_CHECK();
-            tb2 = L.cubtmp_bytes;
-            EVX_CUDA(cub::DeviceRadixSort::SortPairs(P.at<void>(L.cubtmp), tb2, P.at<uint64_t>(L.bkeyA),
-                                                     P.at<uint64_t>(L.bkeyB), idx_nxt, idx_cur, (int)n, 0, 32 + bbits + 5, s));
-            int* t = idx_cur; idx_cur = idx_nxt; idx_nxt = t;
-        }
-        k_block_permute<<<gn, T, 0, s>>>(P.at<float>(L.tcols), idx_nxt, n, L.npad, m, scal, P.at<float>(L.ucols),
-                                         P.at<int>(L.label));
-        EVX_LAUNCH_CHECK();
-        k_relabel_rows<<<gn, T, 0, s>>>(P.at<int>(L.row2u), P.at<int>(L.label), n);
-        EVX_LAUNCH_CHECK();
-    }
+    // labels: block-local f1 order, word-local f2 order (one CTA per block)
+    k_block_labels<<<(unsigned)L.np, TW, 0, s>>>(P.at<float>(L.tcols), L.npad, m, scal, P.at<float>(L.ucols),
+                                                 P.at<int>(L.label));
+    EVX_LAUNCH_CHECK();
+    k_relabel_rows<<<gn, T, 0, s>>>(P.at<int>(L.row2u), P.at<int>(L.label), n);
+    EVX_LAUNCH_CHECK();
 
     if (L.npl == 0) return EVX_OK;
     if (m == 3 && L.np > 1) {                          // f2 rank tables of the panels (used by the off-diagonal tiles)
