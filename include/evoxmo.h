@@ -125,6 +125,20 @@ int evx_select_by_rank_f32(const float* pop, const float* fit, const float* fit_
                            int64_t n, int32_t d, int32_t m, int64_t topk, float* out_pop, float* out_fit,
                            int32_t* out_index, void* ws, size_t ws_bytes, void* stream);
 
+/* ---- (f4) SPEA2 fitness and archive truncation ---------------------------------------------------
+ * replaces algorithms/mo/spea2.py:21-37 `cal_fitness(obj)`: fitness[j] = 1 / (d2[j] + 2) + sum of the
+ * strengths s[i] (= rows i dominates) over the rows i dominating j, d2 = distance to the second nearest
+ * other row (sorted-row index floor(sqrt(6)) - 1); and :40-67 `_truncation(obj, k, mask)`: k times
+ * remove the valid row whose nearest valid neighbour is closest (ties: lowest index), keep[i] = row i is
+ * valid and was not removed.  Nothing n x n is stored.  obj: device float32 [n, m]; fitness: device
+ * float32 [n]; mask, keep: device uint8 [n]; k < number of valid rows, as the reference requires.
+ * Asynchronous.                                                                                      */
+size_t evx_spea2_workspace_bytes(int64_t n, int32_t m);
+int evx_spea2_fitness_f32(const float* obj, int64_t n, int32_t m, float* fitness, void* ws, size_t ws_bytes,
+                          void* stream);
+int evx_spea2_truncation_f32(const float* obj, int64_t n, int32_t m, int64_t k, const uint8_t* mask, uint8_t* keep,
+                             void* ws, size_t ws_bytes, void* stream);
+
 /* ---- (a7) DTLZ1..7 evaluate -------------------------------------------------------------------
  * replaces problems/numerical/dtlz.py:48-69, 84-103, 115-145, 152-172, 188-208, 244-265, 303-322
  * `DTLZk.evaluate(state, X)`.  X: device float32 [n, d]; F: device float32 [n, m].  Asynchronous. */

@@ -354,7 +354,7 @@ def spea2_cal_fitness(obj):
     dis = pairwise_euclidean_dist(obj, obj)
     dis[np.arange(n), np.arange(n)] = np.inf
     dis = np.sort(dis, axis=1)
-    kth = int(np.floor(np.sqrt(6))) - 1
+    kth = min(int(np.floor(np.sqrt(6))) - 1, n - 1)       # n = 1: XLA clamps the out-of-range column index
     d = (F32(1) / (dis[:, kth] + F32(2))).astype(F32)
     return (d + r.astype(F32)).astype(F32)
 
