@@ -31,6 +31,9 @@ _SIGNATURES = {
     "evx_spea2_workspace_bytes": (c_sz, [c_i64, c_i32]),
     "evx_spea2_fitness_f32": (ctypes.c_int, [c_vp, c_i64, c_i32, c_vp, c_vp, c_sz, c_vp]),
     "evx_spea2_truncation_f32": (ctypes.c_int, [c_vp, c_i64, c_i32, c_i64, c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "evx_nsga3_associate_f32": (ctypes.c_int, [c_vp, c_vp, c_i64, c_i64, c_i32, c_vp, c_vp, c_vp]),
+    "evx_nsga3_niche_workspace_bytes": (c_sz, [c_i64, c_i64]),
+    "evx_nsga3_niche": (ctypes.c_int, [c_vp, c_i32, c_vp, c_vp, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_sz, c_vp]),
     "evx_eval_dtlz_f32": (ctypes.c_int, [c_i32, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp]),
     "evx_eval_maf1_f32": (ctypes.c_int, [c_vp, c_i64, c_i32, c_i32, c_vp, c_vp]),
     "evx_lsmop_groups": (ctypes.c_int, [c_i32, c_i32, c_vp, c_vp]),

@@ -1,0 +1,290 @@
+// nsga3.cu - NSGA-III's association and niching.
+//
+// Replaces algorithms/mo/nsga3.py:140-147 (association of every solution with its nearest reference
+// direction: `cos_dist` N x R, perpendicular distance, nanargmin / nanmin) and :148-205 (niche counts and
+// the one-survivor-per-iteration `while_loop`, up to pop_size sequential steps, each of which touches
+// several arrays of N elements in the reference).  The normalisation before it (:103-139: ideal point,
+// extreme points, a tiny M x M solve) stays host glue.
+//   associate - one thread per solution, reference directions staged in shared memory already divided
+//               by their norm; nothing N x R is stored.
+//   niche     - the last front's members are sorted by (group, index) once (radix sort); one persistent
+//               CTA then runs the loop: arg-min of the niche counts through per-thread chunk minima (only
+//               the chunk of the group that changed is rescanned), the candidate by smallest distance or
+//               by the caller's random words with jax.random.randint's own arithmetic, updates.
+// The random words are an INPUT (two 32-bit words per loop index, what randint(keys[i], ...) consumes),
+// so the host framework's PRNG stream stays the reference's.
+#include <cub/device/device_radix_sort.cuh>
+
+#include "common.cuh"
+
+namespace evx {
+
+constexpr int AS_T = 256;
+constexpr int AS_TILE = 128;
+
+// group_id[i] = nanargmin_r dist(i, r) (R if every distance is NaN), group_dist[i] = nanmin (NaN then).
+// dist = ||x|| * sqrt(1 - c^2), c = (x / ||x||) . (y_r / ||y_r||)   (utils/common.py:75-80, nsga3.py:140-143)
+__global__ void __launch_bounds__(AS_T)
+k_nsga3_associate(const float* __restrict__ x, const float* __restrict__ ref, int n, int R, int m, int* __restrict__ gid,
+                  float* __restrict__ gdist) {
+    extern __shared__ float tile[];                   // [AS_TILE][m] normalised reference directions
+    const int i = blockIdx.x * AS_T + threadIdx.x;
+    float xn[EVX_MAX_OBJECTIVES];
+    float nx = 0.0f;
+    if (i < n) {
+        float acc = 0.0f;
+        for (int k = 0; k < m; ++k) { const float v = x[(size_t)i * m + k]; acc = __fadd_rn(acc, __fmul_rn(v, v)); }
+        nx = __fsqrt_rn(acc);
+        for (int k = 0; k < m; ++k) xn[k] = __fdiv_rn(x[(size_t)i * m + k], nx);
+    }
+    float best = __int_as_float(0x7FC00000);          // NaN until a number is seen
+    int bi = R;
+    for (int r0 = 0; r0 < R; r0 += AS_TILE) {
+        const int nt = min(AS_TILE, R - r0);
+        __syncthreads();
+        for (int t = threadIdx.x; t < nt; t += AS_T) {
+            const float* y = ref + (size_t)(r0 + t) * m;
+            float acc = 0.0f;
+            for (int k = 0; k < m; ++k) acc = __fadd_rn(acc, __fmul_rn(y[k], y[k]));
+            const float ny = __fsqrt_rn(acc);
+            for (int k = 0; k < m; ++k) tile[t * m + k] = __fdiv_rn(y[k], ny);
+        }
+        __syncthreads();
+        if (i < n) {
+            for (int t = 0; t < nt; ++t) {
+                float c = 0.0f;
+                for (int k = 0; k < m; ++k) c = __fadd_rn(c, __fmul_rn(xn[k], tile[t * m + k]));
+                const float d = __fmul_rn(nx, __fsqrt_rn(__fsub_rn(1.0f, __fmul_rn(c, c))));
+                if (d == d && !(best <= d)) { best = d; bi = r0 + t; }      // first minimum, NaN skipped
+            }
+        }
+    }
+    if (i < n) { gid[i] = bi; gdist[i] = best; }
+}
+
+// ---- niching ------------------------------------------------------------------------------------------
+struct NicheScal { int selected; };
+
+__global__ void k_niche_counts(const int* __restrict__ rank, const int* __restrict__ gid, int n, int R, int last_rank,
+                               int* __restrict__ rho, int* __restrict__ rho_last, uint32_t* __restrict__ keys,
+                               int* __restrict__ vals) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int g = gid[i], r = rank[i];
+    if (g >= 0 && g < R) {
+        if (r < last_rank) atomicAdd(&rho[g], 1);                           // :148-150
+        else if (r == last_rank) atomicAdd(&rho_last[g], 1);                // :151-153
+    }
+    keys[i] = (r == last_rank && g >= 0 && g < R) ? (uint32_t)g : (uint32_t)R;   // candidates first, by group; stable = by index
+    vals[i] = i;
+}
+
+constexpr int NI_T = 1024;
+constexpr int RHO_INF = 0x7FFFFFFF;
+
+// One CTA.  cand[] = last-front members sorted by (group, index); off[g] = first entry of group g.
+__global__ void __launch_bounds__(NI_T)
+k_niche_loop(int* __restrict__ rank, const float* __restrict__ gdist, const int* __restrict__ cand, int n, int R,
+             int last_rank, int pop_size, int* __restrict__ rho, int* __restrict__ rho_last, int* __restrict__ off,
+             uint8_t* __restrict__ taken, const uint32_t* __restrict__ rbits, int* __restrict__ selected_idx,
+             int* __restrict__ nsel_out) {
+    __shared__ int cmin[NI_T], cidx[NI_T];            // per-chunk minimum of rho and its first index
+    __shared__ int wv[32], wi[32];
+    __shared__ int s_sel, s_group;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int chunk = (R + NI_T - 1) / NI_T;
+    // offsets (exclusive scan of rho_last), selected = sum(rho), rho = inf where the group has no candidate (:158-160)
+    {
+        int part = 0, lsum = 0;
+        for (int g = t * chunk; g < min(R, (t + 1) * chunk); ++g) { part += rho_last[g]; lsum += rho[g]; }
+        int incl = part, tot = lsum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += v;
+        }
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) tot += __shfl_xor_sync(0xFFFFFFFFu, tot, o);
+        if (lane == 31) wv[warp] = incl;
+        if (lane == 0) wi[warp] = tot;
+        __syncthreads();
+        int run = incl - part;
+        for (int w = 0; w < warp; ++w) run += wv[w];
+        if (t == 0) { int s = 0; for (int w = 0; w < 32; ++w) s += wi[w]; s_sel = s; }
+        for (int g = t * chunk; g < min(R, (t + 1) * chunk); ++g) {
+            off[g] = run;
+            run += rho_last[g];
+            if (rho_last[g] == 0) rho[g] = RHO_INF;
+        }
+        __syncthreads();
+    }
+    auto rescan = [&](int th) {                       // chunk minimum of thread th's groups (first index on ties)
+        int bv = RHO_INF, bi = 0x7FFFFFFF;
+        for (int g = th * chunk; g < min(R, (th + 1) * chunk); ++g)
+            if (rho[g] < bv) { bv = rho[g]; bi = g; }
+        if (bi == 0x7FFFFFFF && th * chunk < R) bi = th * chunk;            // all inf: first index of the chunk
+        cmin[th] = bv; cidx[th] = bi;
+    };
+    rescan(t);
+    __syncthreads();
+    int selected = s_sel;
+    while (selected < pop_size) {                                           // :196-200
+        // group = argmin(rho), first index (:169)
+        int bv = cmin[t], bi = cidx[t];
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) {
+            const int ov = __shfl_xor_sync(0xFFFFFFFFu, bv, o), oi = __shfl_xor_sync(0xFFFFFFFFu, bi, o);
+            if (ov < bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+        }
+        if (lane == 0) { wv[warp] = bv; wi[warp] = bi; }
+        __syncthreads();
+        if (warp == 0) {
+            bv = wv[lane]; bi = wi[lane];
+#pragma unroll
+            for (int o = 16; o >= 1; o >>= 1) {
+                const int ov = __shfl_xor_sync(0xFFFFFFFFu, bv, o), oi = __shfl_xor_sync(0xFFFFFFFFu, bi, o);
+                if (ov < bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+            }
+            if (lane == 0) s_group = (bv == RHO_INF) ? -1 : bi;     // -1: no candidate anywhere (cannot happen for pop_size < n)
+        }
+        __syncthreads();
+        const int group = s_group;
+        if (group < 0) break;
+        if (t == 0) {
+            const int first = off[group];
+            const int left = rho_last[group];
+            // the group's entries: cand[first .. first + initial count); find that count lazily while scanning
+            int pick = -1;
+            if (rho[group] == 0 || left == 1) {                             // :187: closest remaining candidate
+                float bd = INFINITY;
+                int seen = 0;
+                for (int q = first; seen < left; ++q) {
+                    if (taken[q]) continue;
+                    ++seen;
+                    const float d = gdist[cand[q]];
+                    if (pick < 0 || d < bd) { bd = d; pick = q; }           // ascending index: first minimum
+                }
+            } else {                                                        // :173-183: the rand_index-th remaining, by index
+                const uint32_t span = (uint32_t)left;
+                const uint32_t hi = rbits[2 * selected], lo = rbits[2 * selected + 1];
+                uint32_t mult = (65536u % span) * (65536u % span);
+                mult %= span;
+                uint32_t offv = (hi % span) * mult + (lo % span);
+                offv %= span;
+                int seen = 0;
+                for (int q = first;; ++q) {
+                    if (taken[q]) continue;
+                    if (seen == (int)offv) { pick = q; break; }
+                    ++seen;
+                }
+            }
+            taken[pick] = 1;
+            rank[cand[pick]] = last_rank - 1;                               // :189
+            rho_last[group] = left - 1;                                     // :191
+            rho[group] = (left - 1 == 0) ? RHO_INF : rho[group] + 1;        // :193-201
+        }
+        __syncthreads();
+        if (t == group / chunk) rescan(t);
+        ++selected;
+        __syncthreads();
+    }
+    // survivors: rank < last_rank, ascending index, first pop_size (:202-204)
+    __shared__ int base;
+    if (t == 0) base = 0;
+    __syncthreads();
+    for (int i0 = 0; i0 < n; i0 += NI_T) {
+        const int i = i0 + t;
+        const bool keep = i < n && rank[i] < last_rank;
+        const uint32_t b = __ballot_sync(0xFFFFFFFFu, keep);
+        if (lane == 0) wv[warp] = __popc(b);
+        __syncthreads();
+        int before = base;
+        for (int w = 0; w < warp; ++w) before += wv[w];
+        const int pos = before + __popc(b & ((1u << lane) - 1u));
+        if (keep && pos < pop_size) selected_idx[pos] = i;
+        __syncthreads();
+        if (t == 0) { int s = 0; for (int w = 0; w < 32; ++w) s += wv[w]; base += s; }
+        __syncthreads();
+    }
+    if (t == 0 && nsel_out) *nsel_out = base;
+}
+
+struct NicheLayout {
+    size_t rank, rho, rho_last, off, keysA, keysB, valsA, valsB, taken, tmp, tmp_bytes, total;
+};
+static NicheLayout niche_layout(int64_t n, int64_t R) {
+    NicheLayout L{};
+    size_t o = 0;
+    auto take = [&](size_t b) { size_t r = o; o = align_up(o + b, 256); return r; };
+    L.rank = take(sizeof(int) * (size_t)n);
+    L.rho = take(sizeof(int) * (size_t)(R + 1));
+    L.rho_last = take(sizeof(int) * (size_t)(R + 1));
+    L.off = take(sizeof(int) * (size_t)(R + 1));
+    L.keysA = take(sizeof(uint32_t) * (size_t)n);
+    L.keysB = take(sizeof(uint32_t) * (size_t)n);
+    L.valsA = take(sizeof(int) * (size_t)n);
+    L.valsB = take(sizeof(int) * (size_t)n);
+    L.taken = take((size_t)n);
+    cub::DeviceRadixSort::SortPairs(nullptr, L.tmp_bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, (const int*)nullptr,
+                                    (int*)nullptr, (int)n);
+    L.tmp = take(L.tmp_bytes);
+    L.total = o;
+    return L;
+}
+
+}  // namespace evx
+
+using namespace evx;
+
+extern "C" int evx_nsga3_associate_f32(const float* normalized, const float* ref, int64_t n, int64_t nref, int32_t m,
+                                       int32_t* group_id, float* group_dist, void* stream) {
+    EVX_REQUIRE(n >= 0 && nref >= 1 && nref < 0x7FFFFFFF && n < 0x7FFFFFFF && m >= 1 && m <= EVX_MAX_OBJECTIVES, EVX_ERR_ARG,
+                "evx_nsga3_associate_f32: bad shape n=%lld nref=%lld m=%d", (long long)n, (long long)nref, m);
+    if (n == 0) return EVX_OK;
+    EVX_REQUIRE(normalized && ref && group_id && group_dist, EVX_ERR_ARG, "evx_nsga3_associate_f32: null pointer");
+    k_nsga3_associate<<<(unsigned)ceil_div(n, AS_T), AS_T, sizeof(float) * AS_TILE * m, (cudaStream_t)stream>>>(
+        normalized, ref, (int)n, (int)nref, m, group_id, group_dist);
+    EVX_LAUNCH_CHECK();
+    return EVX_OK;
+}
+
+extern "C" size_t evx_nsga3_niche_workspace_bytes(int64_t n, int64_t nref) {
+    if (n < 1 || nref < 1 || n >= 0x7FFFFFFF || nref >= 0x7FFFFFFF) return 0;
+    return niche_layout(n, nref).total + 256;
+}
+
+extern "C" int evx_nsga3_niche(const int32_t* rank, int32_t last_rank, const int32_t* group_id, const float* group_dist,
+                               int64_t n, int64_t nref, int64_t pop_size, const uint32_t* rand_words, int32_t* selected_idx,
+                               void* ws, size_t ws_bytes, void* stream) {
+    const size_t need = evx_nsga3_niche_workspace_bytes(n, nref);
+    EVX_REQUIRE(need != 0, EVX_ERR_ARG, "evx_nsga3_niche: bad shape n=%lld nref=%lld", (long long)n, (long long)nref);
+    EVX_REQUIRE(pop_size >= 1 && pop_size < n, EVX_ERR_ARG, "evx_nsga3_niche: pop_size=%lld must be in [1, n)", (long long)pop_size);
+    EVX_REQUIRE(rank && group_id && group_dist && rand_words && selected_idx, EVX_ERR_ARG, "evx_nsga3_niche: null pointer");
+    EVX_REQUIRE(ws && ws_bytes >= need, EVX_ERR_WORKSPACE, "evx_nsga3_niche: workspace %zu < required %zu", ws_bytes, need);
+    cudaStream_t s = (cudaStream_t)stream;
+    char* base = reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(ws), 256));
+    const NicheLayout L = niche_layout(n, nref);
+    int* rk = reinterpret_cast<int*>(base + L.rank);
+    int* rho = reinterpret_cast<int*>(base + L.rho);
+    int* rho_last = reinterpret_cast<int*>(base + L.rho_last);
+    int* off = reinterpret_cast<int*>(base + L.off);
+    uint32_t* kA = reinterpret_cast<uint32_t*>(base + L.keysA);
+    uint32_t* kB = reinterpret_cast<uint32_t*>(base + L.keysB);
+    int* vA = reinterpret_cast<int*>(base + L.valsA);
+    int* vB = reinterpret_cast<int*>(base + L.valsB);
+    uint8_t* taken = reinterpret_cast<uint8_t*>(base + L.taken);
+    EVX_CUDA(cudaMemcpyAsync(rk, rank, sizeof(int) * (size_t)n, cudaMemcpyDeviceToDevice, s));
+    EVX_CUDA(cudaMemsetAsync(rho, 0, sizeof(int) * (size_t)(nref + 1), s));
+    EVX_CUDA(cudaMemsetAsync(rho_last, 0, sizeof(int) * (size_t)(nref + 1), s));
+    EVX_CUDA(cudaMemsetAsync(taken, 0, (size_t)n, s));
+    k_niche_counts<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(rk, group_id, (int)n, (int)nref, last_rank, rho, rho_last, kA, vA);
+    EVX_LAUNCH_CHECK();
+    int bits = 1;
+    while ((1ll << bits) <= nref) ++bits;
+    size_t tb = L.tmp_bytes;
+    EVX_CUDA(cub::DeviceRadixSort::SortPairs(base + L.tmp, tb, kA, kB, vA, vB, (int)n, 0, bits, s));
+    k_niche_loop<<<1, NI_T, 0, s>>>(rk, group_dist, vB, (int)n, (int)nref, last_rank, (int)pop_size, rho, rho_last, off, taken,
+                                    rand_words, selected_idx, nullptr);
+    EVX_LAUNCH_CHECK();
+    return EVX_OK;
+}

@@ -139,6 +139,25 @@ int evx_spea2_fitness_f32(const float* obj, int64_t n, int32_t m, float* fitness
 int evx_spea2_truncation_f32(const float* obj, int64_t n, int32_t m, int64_t k, const uint8_t* mask, uint8_t* keep,
                              void* ws, size_t ws_bytes, void* stream);
 
+/* ---- (f3) NSGA-III association and niching -------------------------------------------------------
+ * replaces algorithms/mo/nsga3.py:140-147: group_id[i] = nearest reference direction of row i by
+ * perpendicular distance ||x|| * sqrt(1 - cos^2) (`cos_dist`, utils/common.py:75-80), group_dist[i] = that
+ * distance; a row of NaN (beyond the last front) gets group nref and distance NaN.
+ * normalized: device float32 [n, m]; ref: device float32 [nref, m].  Asynchronous.                   */
+int evx_nsga3_associate_f32(const float* normalized, const float* ref, int64_t n, int64_t nref, int32_t m,
+                            int32_t* group_id, float* group_dist, void* stream);
+/* replaces nsga3.py:148-205: niche counts of the fronts before `last_rank`, then the niche-preserving
+ * fill from the last front, one survivor per step (the reference's while_loop), and the final index list.
+ * rank: device int32 [n] (not modified); rand_words: device uint32 [2 * (pop_size + 1)], words (2i, 2i+1)
+ * = the two 32-bit draws jax.random.randint(keys[i], (), 0, span) consumes, keys = split(state.key,
+ * pop_size + 1) (:165) - the caller supplies them so that the PRNG stream stays the host framework's;
+ * selected_idx: device int32 [pop_size], ascending row numbers of the survivors.  1 <= pop_size < n.
+ * Asynchronous.                                                                                      */
+size_t evx_nsga3_niche_workspace_bytes(int64_t n, int64_t nref);
+int evx_nsga3_niche(const int32_t* rank, int32_t last_rank, const int32_t* group_id, const float* group_dist,
+                    int64_t n, int64_t nref, int64_t pop_size, const uint32_t* rand_words, int32_t* selected_idx,
+                    void* ws, size_t ws_bytes, void* stream);
+
 /* ---- (a7) DTLZ1..7 evaluate -------------------------------------------------------------------
  * replaces problems/numerical/dtlz.py:48-69, 84-103, 115-145, 152-172, 188-208, 244-265, 303-322
  * `DTLZk.evaluate(state, X)`.  X: device float32 [n, d]; F: device float32 [n, m].  Asynchronous. */

@@ -70,3 +70,30 @@ def normal(key, shape):
     lo = np.nextafter(np.float32(-1.0), np.float32(0.0))
     u = uniform(key, shape, lo, 1.0)
     return (np.float32(np.sqrt(2.0)) * erfinv(u.astype(np.float64)).astype(np.float32)).astype(np.float32)
+
+
+def split(key, num=2):
+    """jax.random.split for the default (non-partitionable) threefry keys: `num` new keys, row i =
+    words (2i, 2i+1) of the key's bit stream of shape (num, 2)."""
+    b = random_bits(key, (num, 2))
+    return [(b[i, 0], b[i, 1]) for i in range(num)]
+
+
+def randint_bits(key):
+    """The two 32-bit words jax.random.randint(key, (), lo, hi) consumes: k1, k2 = split(key);
+    higher = bits(k1), lower = bits(k2)."""
+    k1, k2 = split(key, 2)
+    return int(random_bits(k1, ())), int(random_bits(k2, ()))
+
+
+def randint_from_bits(higher, lower, minval, maxval):
+    """jax.random.randint's arithmetic for 32-bit integers (jax._src.random._randint): uint32 wrap-around,
+    span = maxval - minval (1 if not positive), multiplier = (2^16 mod span)^2 mod span."""
+    span = (maxval - minval) & 0xFFFFFFFF
+    if maxval <= minval:
+        span = 1
+    mult = ((65536 % span) * (65536 % span)) & 0xFFFFFFFF
+    mult %= span
+    off = (((higher % span) * mult) & 0xFFFFFFFF) + (lower % span)
+    off = (off & 0xFFFFFFFF) % span
+    return minval + off

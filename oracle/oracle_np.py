@@ -440,3 +440,105 @@ def nsga2_variation(pop, lb, ub, pro_c, dis_c, pro_m, dis_m, seed, generation):
     c = simulated_binary(pop, dr["sbx_mu"], dr["sbx_sign"], dr["sbx_keep"], dr["sbx_pair"], pro_c, dis_c)
     c = polynomial(c, lb, ub, dr["pm_site"], dr["pm_mu"], pro_m, dis_m)
     return np.clip(c, np.asarray(lb, F32), np.asarray(ub, F32)).astype(F32)
+
+
+# --------------------------------------------------------------------------- #
+# NSGA-III environmental selection         algorithms/mo/nsga3.py:97-205
+# --------------------------------------------------------------------------- #
+def cos_dist(x, y):
+    """utils/common.py:75-80."""
+    x = np.asarray(x, F32)
+    y = np.asarray(y, F32)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        xn = (x / np.linalg.norm(x, axis=-1, keepdims=True)).astype(F32)
+        yn = (y / np.linalg.norm(y, axis=-1, keepdims=True)).astype(F32)
+    return np.dot(xn, yn.T).astype(F32)
+
+
+def nsga3_normalize(merged_fitness, rank, last_rank):
+    """nsga3.py:103-139: NaN out the rows past the last front, shift by the ideal point, find the
+    extreme points, intercepts of their hyperplane (or the worst point when they are degenerate)."""
+    import warnings
+    fit = np.asarray(merged_fitness, F32)
+    m = fit.shape[1]
+    with np.errstate(invalid="ignore", divide="ignore"), warnings.catch_warnings():
+        warnings.simplefilter("ignore")                       # all-NaN rows are part of the algorithm
+        ranked = np.where((rank <= last_rank)[:, None], fit, F32(np.nan)).astype(F32)          # :103-107
+        ideal = np.nanmin(ranked, axis=0)                                                     # :110
+        ranked = (ranked - ideal).astype(F32)
+        weight = (np.eye(m, dtype=F32) + F32(1e-6)).astype(F32)                               # :112
+        extreme_ind = np.array([np.nanargmin(np.nanmax((ranked / weight[i]).astype(F32), axis=1)) for i in range(m)])   # :114-117
+        extreme = ranked[extreme_ind]
+        if np.linalg.matrix_rank(extreme) == m:                                               # :133
+            plane = np.linalg.solve(extreme, np.ones(m, F32)).astype(F32)                     # :123
+            nadir = (F32(1) / plane).astype(F32)
+        else:
+            nadir = np.nanmax(ranked, axis=0)                                                 # :130
+        return (ranked / nadir).astype(F32)                                                   # :139
+
+
+def nsga3_associate(normalized, ref):
+    """nsga3.py:140-147: perpendicular distance to every reference direction, nearest one per row.
+    Rows of NaN (past the last front) get group len(ref) and distance NaN."""
+    ref = np.asarray(ref, F32)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        c = cos_dist(normalized, ref)
+        dist = (np.linalg.norm(normalized, axis=-1, keepdims=True).astype(F32) * np.sqrt(F32(1) - (c * c).astype(F32))).astype(F32)
+    allnan = np.isnan(dist).all(axis=1)
+    gid = np.where(allnan, len(ref), np.nanargmin(np.where(allnan[:, None], F32(0), dist), axis=1)).astype(np.int32)
+    with np.errstate(invalid="ignore"), __import__("warnings").catch_warnings():
+        __import__("warnings").simplefilter("ignore")
+        gdist = np.nanmin(dist, axis=1).astype(F32)
+    return gid, gdist
+
+
+def nsga3_niche(rank, last_rank, group_id, group_dist, nref, pop_size, rbits):
+    """nsga3.py:148-205: niche-preserving fill of the last front.  rbits[i] = (higher, lower) words that
+    `jax.random.randint(keys[i], ...)` would consume (oracle/jax_prng.randint_bits).  Returns the indices
+    of the survivors, ascending (:202-204)."""
+    from . import jax_prng
+    rank = np.array(rank, np.int64, copy=True)
+    n = rank.shape[0]
+    last = rank == last_rank
+    rho = np.bincount(np.where(rank < last_rank, group_id, nref), minlength=nref + 1)[:nref].astype(np.float64)
+    rho_last = np.bincount(np.where(last, group_id, nref), minlength=nref + 1)[:nref].astype(np.int64)
+    gid = np.where(last, group_id.astype(np.float64), np.inf)
+    gdist = np.where(last, group_dist.astype(np.float64), np.inf)
+    selected = int(rho.sum())
+    rho = np.where(rho_last == 0, np.inf, rho)
+    while selected < pop_size:
+        group = int(np.argmin(rho))
+        cand = np.where(gid == group, gdist, np.inf)
+        if rho[group] == 0 or rho_last[group] == 1:
+            c = int(np.argmin(cand))
+        else:
+            order = np.sort(np.where(np.isinf(cand), np.inf, np.arange(n)))
+            hi, lo = rbits[selected]
+            c = int(order[jax_prng.randint_from_bits(hi, lo, 0, int(rho_last[group]))])
+        rank[c] = last_rank - 1
+        gid[c] = np.nan
+        rho_last[group] -= 1
+        if rho_last[group] == 0:
+            rho[group] = np.inf
+        else:
+            rho[group] += 1
+        selected += 1
+    return np.nonzero(rank < last_rank)[0][:pop_size].astype(np.int32)
+
+
+def nsga3_tell(merged_pop, merged_fitness, ref, pop_size, key):
+    """NSGA3.tell, nsga3.py:97-210, on an already merged population.  `key` = (hi, lo) words of the
+    state's PRNG key.  Returns (population, fitness, intermediates)."""
+    from . import jax_prng
+    fit = np.asarray(merged_fitness, F32)
+    rank = non_dominated_sort(fit)
+    order = np.argsort(rank, kind="stable")
+    last_rank = int(rank[order[pop_size]])                                                    # :101 (index pop_size)
+    normalized = nsga3_normalize(fit, rank, last_rank)
+    gid, gdist = nsga3_associate(normalized, ref)
+    keys = jax_prng.split(key, pop_size + 1)                                                  # :165
+    rbits = [jax_prng.randint_bits(k) for k in keys]
+    sel = nsga3_niche(rank, last_rank, gid, gdist, len(ref), pop_size, rbits)
+    return np.asarray(merged_pop)[sel], fit[sel], {"rank": rank, "last_rank": last_rank, "normalized": normalized,
+                                                   "group_id": gid, "group_dist": gdist, "rbits": np.array(rbits, np.uint32),
+                                                   "selected": sel}
