@@ -393,14 +393,20 @@ def operator_rates(torch, hbm_peak):
     import evox_b200 as E
     g = torch.Generator(device="cuda").manual_seed(1)
 
-    def med(fn, reps=10):
+    def med(fn, reps=10, inner=10):
+        """Median over `reps` of the device time of `inner` back-to-back calls / inner: what the stream
+        sustains (a single call between two events mostly measures the host side of the launch)."""
         for _ in range(3):
             fn()
         ts = []
         for _ in range(reps):
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(); fn(); e1.record(); torch.cuda.synchronize()
-            ts.append(e0.elapsed_time(e1))
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(inner):
+                fn()
+            e1.record(); torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1) / inner)
         ts.sort()
         return ts[len(ts) // 2] * 1e-3
 
