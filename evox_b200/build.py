@@ -42,7 +42,28 @@ def build(verbose=False, force=False):
                            capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    build_ffi()
     return OUT
+
+
+def build_ffi():
+    """XLA FFI handlers (evox_b200/ffi/ffi_evoxmo.cc -> libevoxmo_ffi.so), only where JAX and its FFI
+    headers exist.  Neither the build image nor the GPU box of this repo has JAX: there this is a no-op."""
+    try:
+        import jax
+        inc = jax.ffi.include_dir()
+    except Exception:
+        return None
+    src = HERE / "ffi" / "ffi_evoxmo.cc"
+    out = HERE / "libevoxmo_ffi.so"
+    if not _stale(out, [src, OUT]):
+        return out
+    cmd = ["g++", "-O2", "-std=c++17", "-shared", "-fPIC", f"-I{inc}", f"-I{HERE.parent / 'include'}",
+           "-I/usr/local/cuda/include", str(src), "-o", str(out), f"-L{HERE}", "-levoxmo", f"-Wl,-rpath,{HERE}"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"FFI handler build failed:\n{r.stdout}\n{r.stderr}")
+    return out
 
 
 if __name__ == "__main__":
