@@ -76,7 +76,7 @@ struct Scal {
     int fronts;     // persistent peel: number of fronts found (-1: a peer timed out)
     unsigned int arrived;   // persistent peel, one GPU: panels published so far in this launch (see PeerState::arrived)
     unsigned int ctas_done; // fused multi-rank peel: CTA arrivals at the end of a front, all fronts of this launch
-    unsigned long long dbg[8];   // persistent peel: ns spent by CTA 0 / last CTA in accumulate, merge+commit, barrier
+    unsigned long long dbg[16];  // persistent peel: ns spent by CTA 0 / last CTA in accumulate, merge+commit, waiting (see evx_debug_peel_times)
 };
 
 struct Layout {
@@ -1067,9 +1067,11 @@ struct Planes {
 // front f+2 only after it has seen every rank's sizes of front f+1, and a rank publishes its last size
 // of front f+1 only after its last read of front f.
 // So that waiting CTAs do not hammer the size words, every CTA adds the number of panels it published
-// to a counter on every rank (one relaxed reduction per rank); one thread per CTA polls its own GPU's
-// counter and the CTA looks at the size words when the counter says they should all be there.  The
-// counter is a hint only: validity is decided by the words themselves.
+// to a counter on its own GPU, and the CTA that finishes a front last on a GPU stores the front's epoch
+// into its rank's slot on every peer (a plain store: atomics across NVLink cost several microseconds
+// each).  One warp per CTA polls the local counter and the peers' slots, and the CTA looks at the size
+// words when those say they should all be there.  Counter and slots are hints only: validity is decided
+// by the words themselves.
 // Epochs and the counter run on across launches (PeerState::epoch_base / arrived_base; every rank
 // passes the same number of fronts), so stale words never validate and the next launch needs neither a
 // reset nor a host-level hand-shake: the buffer is cleared once, by evx_nds_shard_peer_init.
@@ -1077,9 +1079,10 @@ constexpr int MAX_WORLD = 8;
 struct PeerState {
     int abort;                              // a rank gave up waiting (4 s): everybody leaves
     unsigned int epoch_base;                // epoch of the last front of the previous launch (local use only)
-    unsigned int arrived;                   // panels published to this replica so far, all launches (a hint)
+    unsigned int arrived;                   // panels this rank's CTAs have published so far, all launches (a hint, local)
     unsigned int arrived_base;              // its value when the previous launch was complete (local use only)
-    unsigned int pad[60];
+    unsigned int done_epoch[MAX_WORLD];     // [r]: last front epoch rank r has published completely (a hint, written by rank r)
+    unsigned int pad[52];
 };
 static_assert(sizeof(PeerState) == 256, "PeerState must stay 256 bytes");
 struct PeerTable {
@@ -1336,10 +1339,9 @@ __device__ __forceinline__ void peel_commit_seg(uint32_t* cp, int K, Delta delta
 // End of a CTA's work on a front: publish the size words of the panels it committed (after one fence
 // that covers every warp's planes, ranks and members), then tell every rank how many panels this CTA
 // has published for the coming front.
-// `call` = how many times this CTA has been here in this launch (1 = after the init), `nlocal` = live
-// panels this rank owns.  Fused multi-rank: every CTA adds its panels to the LOCAL counter; the CTA that
-// arrives last on this GPU adds the rank's whole share to every peer's counter - 7 reductions cross
-// NVLink per front and rank instead of 7 per CTA (2 000 same-address atomics per front and GPU).
+// `call` = how many times this CTA has been here in this launch (1 = after the init).  Fused multi-rank:
+// every CTA adds its panels to the LOCAL counter; the CTA that arrives last on this GPU stores the
+// front's epoch into the rank's slot on every peer.
 template <bool MULTI>
 __device__ __forceinline__ void publish_pending(PubList* pub, FWord* cnt_next, unsigned int fe_next, Scal* scal,
                                                 const PeerTable& pt, unsigned int call, unsigned int nlocal) {
@@ -1357,10 +1359,10 @@ __device__ __forceinline__ void publish_pending(PubList* pub, FWord* cnt_next, u
             if (pt.world > 1) {
                 unsigned int old;
                 asm volatile("atom.relaxed.gpu.global.add.u32 %0, [%1], 1;" : "=r"(old) : "l"(&scal->ctas_done) : "memory");
-                if (old + 1u == call * gridDim.x && nlocal)
+                if (old + 1u == call * gridDim.x)                          // last CTA of this GPU to finish the front
                     for (int r = 0; r < pt.world; ++r)
                         if (r != pt.rank)
-                            asm volatile("red.relaxed.sys.global.add.u32 [%0], %1;" ::"l"(&peer_state(pt, r)->arrived), "r"(nlocal) : "memory");
+                            asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(&peer_state(pt, r)->done_epoch[pt.rank]), "r"(fe_next) : "memory");
             }
         } else {
             if (total) asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(&scal->arrived), "r"(total) : "memory");
@@ -1484,7 +1486,7 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
     Ring2 rg;
     rg.slots = &sh.ring[warp][0][0];
     int k = 0;
-    unsigned long long t_acc = 0, t_mc = 0, t_bar = 0, t_mark = global_ns();
+    unsigned long long t_acc = 0, t_mc = 0, t_bar = 0, t_hint = 0, t_scan = 0, t_mark = global_ns();
     for (;; ++k) {
         // ---- the front as a virtual list: pre[J] = members in panels < J; S[q] = cost units before pair q ----
         const unsigned int fe = e0 + (unsigned int)k;              // this front's epoch
@@ -1501,16 +1503,22 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
             int c[2 * DYN_MAX_PPT];
             int psum = 0;
             bool done = false;
-            if (threadIdx.x == 0) {                                 // all npan panels of fronts 0..k published (hint)
-                const unsigned int target = abase + (unsigned int)npan * (unsigned int)(k + 1);
+            if (warp == 0) {                                        // hints: my GPU's panels of fronts 0..k, and every peer done with front k
+                const unsigned int target = abase + nlocal * (unsigned int)(k + 1);
+                const bool peer = MULTI && lane < pt.world && lane != pt.rank;
+                const unsigned int* word = peer ? &peer_state(pt, pt.rank)->done_epoch[lane] : arrived;
+                const unsigned int want = peer ? fe : target;
                 for (unsigned int spin = 0;; ++spin) {
                     unsigned int v;
-                    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(arrived) : "memory");
-                    if ((int)(v - target) >= 0) break;
-                    __nanosleep(32);                                // 300 pollers on one word: leave the L2 slice some air
+                    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(word) : "memory");
+                    if (__all_sync(0xFFFFFFFFu, (int)(v - want) >= 0)) break;
+                    __nanosleep(32);                                // 300 pollers on one line: leave the L2 slice some air
                     if ((spin & 1023u) == 1023u && global_ns() - t_start > PEER_TIMEOUT_NS * (MULTI ? 1 : 8)) break;
                 }
-                asm volatile("fence.acq_rel.gpu;" ::: "memory");    // acquire: the committers' planes and members
+                if (lane == 0) {
+                    asm volatile("fence.acq_rel.gpu;" ::: "memory");    // acquire: the committers' planes and members
+                    t_hint += global_ns() - t_mark;
+                }
             }
             __syncthreads();
             for (unsigned int round = 0;; ++round) {
@@ -1608,6 +1616,7 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
             __syncthreads();
         }
         const int nf = pre[npan];
+        if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_scan += t - t_mark; t_acc -= 0; t_mark = t; }
         if (nf <= 0) break;
         const long long T = S[nq];
         const int lo = (int)((long long)B * T / G), hi = (int)((long long)(B + 1) * T / G);
@@ -1791,13 +1800,15 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
         // k + 1 fronts (the last one empty) were published by every rank: the next launch continues from there
         if (B == 0 && threadIdx.x == 0 && k >= 0) {
             peer_state(pt, pt.rank)->epoch_base = e0 + (unsigned int)k;
-            peer_state(pt, pt.rank)->arrived_base = abase + (unsigned int)npan * (unsigned int)(k + 1);
+            peer_state(pt, pt.rank)->arrived_base = abase + nlocal * (unsigned int)(k + 1);
         }
     }
     if (B == 0 && threadIdx.x == 0) scal->fronts = k;
     if (threadIdx.x == 0 && (B == 0 || B == G - 1)) {
         unsigned long long* d = scal->dbg + (B == 0 ? 0 : 4);
         d[0] = t_acc; d[1] = t_mc; d[2] = t_bar; d[3] = (unsigned long long)(k > 0 ? k : 1);
+        unsigned long long* e = scal->dbg + (B == 0 ? 8 : 12);
+        e[0] = t_hint; e[1] = t_scan;
     }
 }
 
@@ -2176,8 +2187,7 @@ extern "C" int evx_debug_peel_times(evx_nds_shard* p, uint64_t* out8) {
         return EVX_OK;
     }
     Scal* scal = p->P.at<Scal>(p->P.L.scal);
-    memset(out8, 0, sizeof(uint64_t) * 16);
-    EVX_CUDA(cudaMemcpy(out8, scal->dbg, sizeof(uint64_t) * 8, cudaMemcpyDeviceToHost));
+    EVX_CUDA(cudaMemcpy(out8, scal->dbg, sizeof(uint64_t) * 16, cudaMemcpyDeviceToHost));
     return EVX_OK;
 }
 
@@ -2261,7 +2271,7 @@ extern "C" int evx_nds_f32(const float* x, int64_t n, int32_t m, int32_t* rank, 
         EVX_CUDA(cudaEventElapsedTime(&pf.prep_ms, pf.ev[0], pf.ev[1]));
         EVX_CUDA(cudaEventElapsedTime(&pf.tiles_ms, pf.ev[1], pf.ev[2]));
         EVX_CUDA(cudaEventElapsedTime(&pf.peel_ms, pf.ev[2], pf.ev[3]));
-        EVX_CUDA(cudaMemcpy(g_dbg_times, scal->dbg, sizeof(uint64_t) * 8, cudaMemcpyDeviceToHost));
+        EVX_CUDA(cudaMemcpy(g_dbg_times, scal->dbg, sizeof(uint64_t) * 16, cudaMemcpyDeviceToHost));
         pf.have = true;
     }
     return EVX_OK;

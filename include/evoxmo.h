@@ -235,7 +235,8 @@ void evx_profile_enable(int32_t on);
 int evx_profile_last(float* prep_ms, float* tiles_ms, float* peel_ms);
 /* nanoseconds the persistent peel kernel of the plan's last run spent in {gathering, merge + commit +
  * publish, waiting for the next front's sizes, number of fronts} as seen by its first CTA (out16[0..3])
- * and its last CTA (out16[4..7]); out16[8..15] are zero.  p == NULL: the values of this host thread's
+ * and its last CTA (out16[4..7]); out16[8..9] / out16[12..13]: of the waiting time, the part until the arrival counter
+ * said "complete", and the time of the two scans that follow (first / last CTA).  p == NULL: the values of this host thread's
  * last evx_nds_f32 call made with evx_profile_enable(1).                                            */
 int evx_debug_peel_times(evx_nds_shard* p, uint64_t* out16);
 #ifdef __cplusplus

@@ -39,6 +39,6 @@ if rank == 0:
     check(L.evx_debug_peel_times(f.shard.plan, dbg))
     for nm, o in (("first CTA", 0), ("last CTA", 4)):
         k = max(1, dbg[o + 3])
-        print(f"{nm}: per front  accumulate {dbg[o]/k/1e3:7.2f} us  merge+commit {dbg[o+1]/k/1e3:6.2f} us  wait for next front {dbg[o+2]/k/1e3:6.2f} us")
+        print(f"{nm}: per front  accumulate {dbg[o]/k/1e3:7.2f} us  merge+commit {dbg[o+1]/k/1e3:6.2f} us  wait for next front {dbg[o+2]/k/1e3:6.2f} us (until the hint {dbg[8 + o]/k/1e3:5.2f})  scans {dbg[9 + o]/k/1e3:5.2f} us")
     print("fronts", f.num_fronts, "world", world, "n", n, flush=True)
 dist.destroy_process_group()

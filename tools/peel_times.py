@@ -21,4 +21,4 @@ for n in sizes:
     print(f"n {n} prep {a.value:.3f} tiles {b.value:.3f} peel {c.value:.3f} ms")
     for nm, o in (("first CTA", 0), ("last CTA", 4)):
         k = max(1, dbg[o + 3])
-        print(f"{nm}: fronts {k} per front: accumulate {dbg[o]/k/1e3:7.2f} us  merge+commit {dbg[o+1]/k/1e3:6.2f} us  scan+barrier {dbg[o+2]/k/1e3:6.2f} us")
+        print(f"{nm}: fronts {k} per front: accumulate {dbg[o]/k/1e3:7.2f} us  merge+commit {dbg[o+1]/k/1e3:6.2f} us  wait {dbg[o+2]/k/1e3:6.2f} us (until the hint {dbg[8 + o]/k/1e3:5.2f})  scans {dbg[9 + o]/k/1e3:5.2f} us")
