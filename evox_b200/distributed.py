@@ -15,6 +15,23 @@ from ._dev import as_f32_cuda, stream_ptr
 from ._lib import EvoxMoError, check, lib
 
 
+def recommended_world(n, available=8):
+    """How many GPUs to give one non-dominated sort of n rows (measured on 8 x B200, profiles/r2_scaling.md):
+    the bit matrix shrinks as 1/G but every front costs one exchange across all GPUs, so small populations
+    with many light fronts are fastest on one GPU (N = 200k: 3.50 ms on one, 3.55 on two, 4.57 on eight),
+    while N = 1M gains up to eight (31.2 -> 10.4 ms)."""
+    if n < 300_000:
+        want = 1
+    elif n < 500_000:
+        want = 2
+    else:
+        want = available
+    w = 1
+    while w * 2 <= min(want, available):
+        w *= 2
+    return w
+
+
 class _CudaShard:
     """Device side of one rank: thin wrapper over the evx_nds_shard_* entry points."""
 
