@@ -68,3 +68,47 @@ def test_panel_ownership_covers_every_column_once():
             owners += s._owned(np.arange(n))
             assert s.mask_words * 32 >= int(s._owned(np.arange(n)).sum())
         assert (owners == 1).all()
+
+
+# ---- the evaluation shard of the N-GPU NSGA-II generation (std_workflow.py:187-200 + core/distributed.py:49-56) ----
+class _CpuProblem:
+    """Stand-in problem on CPU tensors (the CUDA evaluate is covered by the -m gpu tests): a row-wise
+    function, so slicing rows and gathering must reproduce the unsharded result exactly."""
+
+    def evaluate(self, state, X):
+        return torch.stack([X.sum(1), (X * X).sum(1), X[:, 0] - X[:, -1]], dim=1), state
+
+
+def _eval_worker(rank, world, port, n, d, q):
+    sys.path.insert(0, str(ROOT))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from evox_b200.distributed import recommended_world, sharded_evaluate
+        X = torch.from_numpy(np.random.default_rng(9).random((n, d), dtype=np.float32))
+        state = object()
+        F, st = sharded_evaluate(_CpuProblem(), state, X)
+        q.put((rank, F.numpy().copy(), st is state, recommended_world(200_000), recommended_world(1_000_000, world)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n", [(2, 1000), (2, 1001), (3, 10), (2, 1)])
+def test_sharded_evaluate_matches_unsharded(world, n):
+    """Rows dealt in equal slices, all-gather of the fitness; a population that does not divide by the world
+    size (ragged last slice, even an empty one) gives the same F on every rank as one evaluate call."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + (os.getpid() + n + world) % 2000
+    procs = [ctx.Process(target=_eval_worker, args=(r, world, port, n, 5, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=300) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    X = torch.from_numpy(np.random.default_rng(9).random((n, 5), dtype=np.float32))
+    want, _ = _CpuProblem().evaluate(None, X)
+    for rank, F, same_state, w_small, w_big in results:
+        assert F.shape == (n, 3) and (F == want.numpy()).all(), rank
+        assert same_state and w_small == 1 and w_big == (2 if world >= 2 else 1)
