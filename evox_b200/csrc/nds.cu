@@ -1858,10 +1858,13 @@ static int launch_tiles(const Plan& P, cudaStream_t s) {
                                                                   P.at<int>(L.count), L.world, L.rank, slabs_off);
         EVX_LAUNCH_CHECK();
     }
-    dim3 gdiag((unsigned)ceil_div(TW, slabs * TILE_WARPS * SLAB), (unsigned)L.npl);
+    // diagonal blocks: one slab per warp, i.e. TW / 256 CTAs per block - there are only NP blocks, and a
+    // CTA with four slabs per warp left one CTA per SM at N = 200k (0.127 ms; the full compare is the slow path)
+    const int slabs_diag = 1;
+    dim3 gdiag((unsigned)ceil_div(TW, slabs_diag * TILE_WARPS * SLAB), (unsigned)L.npl);
     k_dominance_diag<M><<<gdiag, TILE_WARPS * 32, smem_diag, s>>>(P.at<float>(L.ucols), L.npad, P.at<Scal>(L.scal),
                                                                    P.at<uint32_t>(L.bits), P.at<int>(L.count), L.world,
-                                                                   L.rank, slabs);
+                                                                   L.rank, slabs_diag);
     EVX_LAUNCH_CHECK();
     return EVX_OK;
 }
