@@ -15,7 +15,7 @@ constexpr int REL_CPT = 16;      // y columns per thread (16 bytes of output per
 // out[i, j] byte matrix.  Thread <-> 16 consecutive columns whose M objectives sit in registers
 // (M <= 4; larger M re-reads them through L1), CTA <-> 32 rows staged in shared memory and broadcast.
 // Each warp writes 512 contiguous bytes of one output row per step: the kernel is bound by the
-// nx*ny-byte store stream the reference API demands, then by FSETP issue (2*M compares per pair).
+// nx*ny-byte store stream the reference API demands, then by issue (2*M sign-bit compares per pair).
 template <int M>
 __global__ void __launch_bounds__(REL_TX)
 k_relation_u8(const float* __restrict__ x, int64_t nx, const float* __restrict__ y, int64_t ny, int m_rt,
@@ -31,27 +31,42 @@ k_relation_u8(const float* __restrict__ x, int64_t nx, const float* __restrict__
     const int ncol = (int)min((int64_t)REL_CPT, ny - j0);
     const bool vec_ok = (ncol == REL_CPT) && ((ny & 15) == 0) && ((reinterpret_cast<size_t>(out) & 15) == 0);
     if constexpr (M > 0) {
+        // Compares on the FMA pipe: for values without NaN and with -0 folded onto +0, b - a has its sign bit
+        // set iff b < a (inf - inf is the canonical positive NaN: "not below"), so
+        //   all_k(a_k <= b_k)  <=>  sign(OR_k (b_k - a_k)) == 0,     any_k(a_k < b_k)  <=>  sign(OR_k (a_k - b_k)) == 1.
+        // Six FADD + three LOP3 per pair instead of six FSETP on the half-rate pipe.  A row or column that
+        // holds a NaN dominates nothing and is dominated by nothing (IEEE compares): masked out at the end.
         float yv[REL_CPT][M];
+        uint32_t cm[4] = {0, 0, 0, 0};                                 // 0x01 per column that exists and holds no NaN
 #pragma unroll
-        for (int c = 0; c < REL_CPT; ++c)
+        for (int c = 0; c < REL_CPT; ++c) {
+            bool ok = c < ncol;
 #pragma unroll
-            for (int k = 0; k < M; ++k)
-                yv[c][k] = (c < ncol) ? __ldg(y + (j0 + c) * M + k) : __int_as_float(0x7FC00000);   // NaN: never dominated
+            for (int k = 0; k < M; ++k) {
+                const float v = (c < ncol) ? __ldg(y + (j0 + c) * M + k) : 0.0f;
+                ok = ok && (v == v);
+                yv[c][k] = v + 0.0f;
+            }
+            cm[c >> 2] |= (uint32_t)ok << (8 * (c & 3));
+        }
         for (int r = 0; r < rows; ++r) {
             float a[M];
+            bool rok = true;
 #pragma unroll
-            for (int k = 0; k < M; ++k) a[k] = xs[r * M + k];
+            for (int k = 0; k < M; ++k) { a[k] = xs[r * M + k] + 0.0f; rok = rok && (a[k] == a[k]); }
             uint32_t pk[4] = {0, 0, 0, 0};
 #pragma unroll
             for (int c = 0; c < REL_CPT; ++c) {
-                bool le = true, ge = true;                            // any(a < b) == !all(a >= b) once all(a <= b) holds
+                uint32_t below = 0u, above = 0u;
 #pragma unroll
                 for (int k = 0; k < M; ++k) {
-                    le = le && (a[k] <= yv[c][k]);
-                    ge = ge && (a[k] >= yv[c][k]);
+                    below |= __float_as_uint(yv[c][k] - a[k]);         // sign: y < x in objective k
+                    above |= __float_as_uint(a[k] - yv[c][k]);         // sign: x < y in objective k
                 }
-                pk[c >> 2] |= (uint32_t)(le && !ge) << (8 * (c & 3));
+                pk[c >> 2] |= ((~below & above) >> 31) << (8 * (c & 3));
             }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) pk[q] = rok ? (pk[q] & cm[q]) : 0u;
             uint8_t* o = out + (row0 + r) * ny + j0;
             if (vec_ok) {
                 *reinterpret_cast<uint4*>(o) = make_uint4(pk[0], pk[1], pk[2], pk[3]);

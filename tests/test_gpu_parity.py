@@ -232,6 +232,21 @@ def test_relation_random(E, nx, ny, m):
         assert ((bits[:, -1] >> np.uint32(ny % 32)) == 0).all()          # tail bits are zero
 
 
+@pytest.mark.parametrize("m", [2, 3, 4, 6])
+def test_relation_special_values(E, m):
+    """The byte-matrix kernel compares by the sign of differences for m <= 4: infinities (inf - inf), signed
+    zeros and NaN in rows and in columns must come out as IEEE compares give them (utils/common.py:88-91)."""
+    from oracle import oracle_c as C
+    rng = np.random.default_rng(40 + m)
+    vals = np.array([0.0, -0.0, 1.0, -1.0, np.inf, -np.inf, np.nan, 0.5, 1e-45, -1e-45], np.float32)
+    x = vals[rng.integers(0, len(vals), (257, m))]
+    y = vals[rng.integers(0, len(vals), (1000, m))]
+    with np.errstate(invalid="ignore"):
+        ref = C.dominate_relation(x, y)
+    d = E.utils.dominate_relation(_cuda(x), _cuda(y)).cpu().numpy()
+    assert (d == ref).all(), np.argwhere(d != ref)[:5]
+
+
 def test_host_rank_from_domination_matrix(E):
     from oracle import oracle_np as O
     from evox_b200.operators.selection.non_dominate import host_rank_from_domination_matrix
