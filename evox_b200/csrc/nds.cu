@@ -727,7 +727,8 @@ __device__ __forceinline__ void tile_offdiag_m3(const uint8_t* __restrict__ ptab
     // the f1 rank masks are read once per row: they stay in global memory (L1) so that five CTAs fit on an SM
     const uint32_t* m1 = reinterpret_cast<const uint32_t*>(ptab + (size_t)(col0 / TW) * PT_BYTES + PT_M1);   // [PW][33]
     uint32_t* wcm = reinterpret_cast<uint32_t*>(sb + PT_M1);               // [PW] valid-column mask of each word
-    uint2* rec = reinterpret_cast<uint2*>(sb + PT_M1 + 4 * PW);            // [TILE_WARPS][32] per-row records
+    uint32_t* seltab = wcm + PW;                                           // [64] byte selectors by (word - ws_r + 32), see below
+    uint4* rec = reinterpret_cast<uint4*>(sb + PT_M1 + 4 * PW + 256);      // [TILE_WARPS][32] per-row records
     uint32_t* flush = smem;                                                // counts_flush scratch: reuses the (then dead) tables
     {
         const uint4* src = reinterpret_cast<const uint4*>(ptab + (size_t)(col0 / TW) * PT_BYTES);
@@ -738,13 +739,21 @@ __device__ __forceinline__ void tile_offdiag_m3(const uint8_t* __restrict__ ptab
         const int ncol = min(32, U - (col0 + (int)threadIdx.x * 32));      // valid columns in this word
         wcm[threadIdx.x] = (ncol >= 32) ? 0xFFFFFFFFu : (ncol <= 0 ? 0u : ((1u << ncol) - 1u));
     }
+    // The f1 decision of word w for a row whose straddle word is ws_r: all pairs fail (w < ws_r), the row's
+    // mask m1 applies (w == ws_r), all pairs pass (w > ws_r).  As a byte selector for PRMT over {m1, 0x000000FF}:
+    // 0x5555 picks the zero byte four times, 0x3210 passes m1 through, 0x4444 picks 0xFF four times - one
+    // shared-memory load (index w - ws_r + 32) and one PRMT instead of two compares and two selects on the
+    // ALU pipe, which is the pipe this kernel saturates.
+    if (threadIdx.x < 64) seltab[threadIdx.x] = threadIdx.x < 32 ? 0x5555u : (threadIdx.x == 32 ? 0x3210u : 0x4444u);
     __syncthreads();
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t f2addr = (uint32_t)__cvta_generic_to_shared(f2s);
     const uint32_t tabaddr = (uint32_t)__cvta_generic_to_shared(sb + PT_TAB);
+    const uint32_t seladdr = (uint32_t)__cvta_generic_to_shared(seltab);
     const uint32_t mywcm = wcm[lane];
-    uint2* myrec = rec + warp * 32;
+    const uint32_t lane4 = 4u * (uint32_t)lane;
+    uint4* myrec = rec + warp * 32;
     const uint32_t recaddr = (uint32_t)__cvta_generic_to_shared(myrec);
     CountPlanes cp;
 
@@ -766,37 +775,44 @@ __device__ __forceinline__ void tile_offdiag_m3(const uint8_t* __restrict__ ptab
             if (sw[k + step - 1] < xf1) k += step;
         if (k == 31 && sw[31] < xf1) k = 32;
         __syncwarp();                                                       // the previous slab's records have been read
-        myrec[lane] = make_uint2(((tabaddr + (uint32_t)g * PW) << 8) | (uint32_t)ws, __ldg(m1 + ws * 33 + k));
+        myrec[lane] = make_uint4(tabaddr + (uint32_t)g * PW, seladdr + 4u * (uint32_t)(32 - ws), __ldg(m1 + ws * 33 + k), 0u);
         __syncwarp();
         // ---- lane <-> word ----
         uint32_t* gout = bits + bits_offset(l, rs, world, rank) + lane;
-#pragma unroll 1
+        uint32_t e8[4];                                                     // carries out of the fours plane, one per 8 rows
+#pragma unroll
         for (int r0 = 0; r0 < 32; r0 += 8) {
             uint32_t v[8];
 #pragma unroll
             for (int t = 0; t < 8; ++t) {
-                uint32_t rp, rm;                                            // (table row address << 8 | ws_r), m1 mask
-                asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(rp), "=r"(rm) : "r"(recaddr + 8u * (uint32_t)(r0 + t)));
-                const uint32_t rw = rp & 0xFFu;
-                uint32_t cnt;                                               // columns of my word with f2 < the row's
-                asm volatile("ld.shared.u8 %0, [%1];" : "=r"(cnt) : "r"((rp >> 8) + (uint32_t)lane));
+                uint32_t ra, rs2, rm, rz;                                   // table row address, selector address of word 0, m1 mask
+                asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(ra), "=r"(rs2), "=r"(rm), "=r"(rz)
+                             : "r"(recaddr + 16u * (uint32_t)(r0 + t)));
+                uint32_t cnt, sel;                                          // columns of my word with f2 < the row's; f1 selector
+                asm volatile("ld.shared.u8 %0, [%1];" : "=r"(cnt) : "r"(ra + (uint32_t)lane));
+                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(sel) : "r"(rs2 + lane4));
                 uint32_t mk;
                 asm("shf.l.clamp.b32 %0, %1, %2, %3;" : "=r"(mk) : "r"(0u), "r"(0xFFFFFFFFu), "r"(cnt));   // ~0 << cnt, 0 at 32
-                const uint32_t keep = (uint32_t)lane > rw ? mywcm : ((uint32_t)lane == rw ? (mywcm & rm) : 0u);
-                v[t] = mk & keep;
+                v[t] = mk & mywcm & __byte_perm(rm, 0xFFu, sel);
             }
 #pragma unroll
             for (int t = 0; t < 8; ++t) gout[(int64_t)(r0 + t) * PW2] = v[t];
-            uint32_t ta, tb, fa, fb, e;
+            uint32_t ta, tb, fa, fb;
             csa(ta, cp.ones, cp.ones, v[0], v[1]);
             csa(tb, cp.ones, cp.ones, v[2], v[3]);
             csa(fa, cp.twos, cp.twos, ta, tb);
             csa(ta, cp.ones, cp.ones, v[4], v[5]);
             csa(tb, cp.ones, cp.ones, v[6], v[7]);
             csa(fb, cp.twos, cp.twos, ta, tb);
-            csa(e, cp.fours, cp.fours, fa, fb);
+            csa(e8[r0 >> 3], cp.fours, cp.fours, fa, fb);
+        }
+        {                                                                   // the slab's four eights-carries: one ripple per slab
+            uint32_t sa, sb2, c32;
+            csa(sa, cp.up[0], cp.up[0], e8[0], e8[1]);
+            csa(sb2, cp.up[0], cp.up[0], e8[2], e8[3]);
+            csa(c32, cp.up[1], cp.up[1], sa, sb2);
 #pragma unroll
-            for (int p = 0; p < TILE_NUP; ++p) { const uint32_t c = cp.up[p] & e; cp.up[p] ^= e; e = c; }
+            for (int p = 2; p < TILE_NUP; ++p) { const uint32_t c = cp.up[p] & c32; cp.up[p] ^= c32; c32 = c; }
         }
     }
     __syncthreads();
@@ -1851,7 +1867,7 @@ static int launch_tiles(const Plan& P, cudaStream_t s) {
     constexpr int SLAB = 32 * tile_rb(M), MAX_SLABS = TILE_ROWS_PER_WARP / SLAB;
     static_assert(TW % (MAX_SLABS * TILE_WARPS * SLAB) == 0, "a CTA's rows must tile a block");
     const size_t stage_words = (size_t)TILE_WARPS * PW * (SLAB + 1);
-    const size_t smem = (M == 3) ? (size_t)PT_M1 + 4 * PW + 8 * 32 * TILE_WARPS
+    const size_t smem = (M == 3) ? (size_t)PT_M1 + 4 * PW + 256 + 16 * 32 * TILE_WARPS
                                  : sizeof(uint32_t) * ((size_t)(M > 1 ? M - 1 : 1) * TW + stage_words + 3 * PW);
     const size_t smem_diag = sizeof(uint32_t) * ((size_t)M * TW + stage_words + TW);
     EVX_CUDA(cudaFuncSetAttribute(k_dominance_tiles<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
