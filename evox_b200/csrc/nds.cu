@@ -728,7 +728,7 @@ __device__ __forceinline__ void tile_offdiag_m3(const uint8_t* __restrict__ ptab
     const uint32_t* m1 = reinterpret_cast<const uint32_t*>(ptab + (size_t)(col0 / TW) * PT_BYTES + PT_M1);   // [PW][33]
     uint32_t* wcm = reinterpret_cast<uint32_t*>(sb + PT_M1);               // [PW] valid-column mask of each word
     uint32_t* seltab = wcm + PW;                                           // [64] byte selectors by (word - ws_r + 32), see below
-    uint4* rec = reinterpret_cast<uint4*>(sb + PT_M1 + 4 * PW + 256);      // [TILE_WARPS][32] per-row records
+    uint2* rec = reinterpret_cast<uint2*>(sb + PT_M1 + 4 * PW + 256);      // [TILE_WARPS][32] per-row records
     uint32_t* flush = smem;                                                // counts_flush scratch: reuses the (then dead) tables
     {
         const uint4* src = reinterpret_cast<const uint4*>(ptab + (size_t)(col0 / TW) * PT_BYTES);
@@ -753,7 +753,7 @@ __device__ __forceinline__ void tile_offdiag_m3(const uint8_t* __restrict__ ptab
     const uint32_t seladdr = (uint32_t)__cvta_generic_to_shared(seltab);
     const uint32_t mywcm = wcm[lane];
     const uint32_t lane4 = 4u * (uint32_t)lane;
-    uint4* myrec = rec + warp * 32;
+    uint2* myrec = rec + warp * 32;
     const uint32_t recaddr = (uint32_t)__cvta_generic_to_shared(myrec);
     CountPlanes cp;
 
@@ -775,7 +775,8 @@ __device__ __forceinline__ void tile_offdiag_m3(const uint8_t* __restrict__ ptab
             if (sw[k + step - 1] < xf1) k += step;
         if (k == 31 && sw[31] < xf1) k = 32;
         __syncwarp();                                                       // the previous slab's records have been read
-        myrec[lane] = make_uint4(tabaddr + (uint32_t)g * PW, seladdr + 4u * (uint32_t)(32 - ws), __ldg(m1 + ws * 33 + k), 0u);
+        // (both shared-memory addresses are below 64 K: the CTA has 44 KB)
+        myrec[lane] = make_uint2((tabaddr + (uint32_t)g * PW) | ((seladdr + 4u * (uint32_t)(32 - ws)) << 16), __ldg(m1 + ws * 33 + k));
         __syncwarp();
         // ---- lane <-> word ----
         uint32_t* gout = bits + bits_offset(l, rs, world, rank) + lane;
@@ -785,9 +786,9 @@ __device__ __forceinline__ void tile_offdiag_m3(const uint8_t* __restrict__ ptab
             uint32_t v[8];
 #pragma unroll
             for (int t = 0; t < 8; ++t) {
-                uint32_t ra, rs2, rm, rz;                                   // table row address, selector address of word 0, m1 mask
-                asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(ra), "=r"(rs2), "=r"(rm), "=r"(rz)
-                             : "r"(recaddr + 16u * (uint32_t)(r0 + t)));
+                uint32_t rp, rm;                                            // table row address | selector address of word 0 << 16, m1 mask
+                asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(rp), "=r"(rm) : "r"(recaddr + 8u * (uint32_t)(r0 + t)));
+                const uint32_t ra = rp & 0xFFFFu, rs2 = rp >> 16;
                 uint32_t cnt, sel;                                          // columns of my word with f2 < the row's; f1 selector
                 asm volatile("ld.shared.u8 %0, [%1];" : "=r"(cnt) : "r"(ra + (uint32_t)lane));
                 asm volatile("ld.shared.u32 %0, [%1];" : "=r"(sel) : "r"(rs2 + lane4));
@@ -1867,7 +1868,7 @@ static int launch_tiles(const Plan& P, cudaStream_t s) {
     constexpr int SLAB = 32 * tile_rb(M), MAX_SLABS = TILE_ROWS_PER_WARP / SLAB;
     static_assert(TW % (MAX_SLABS * TILE_WARPS * SLAB) == 0, "a CTA's rows must tile a block");
     const size_t stage_words = (size_t)TILE_WARPS * PW * (SLAB + 1);
-    const size_t smem = (M == 3) ? (size_t)PT_M1 + 4 * PW + 256 + 16 * 32 * TILE_WARPS
+    const size_t smem = (M == 3) ? (size_t)PT_M1 + 4 * PW + 256 + 8 * 32 * TILE_WARPS
                                  : sizeof(uint32_t) * ((size_t)(M > 1 ? M - 1 : 1) * TW + stage_words + 3 * PW);
     const size_t smem_diag = sizeof(uint32_t) * ((size_t)M * TW + stage_words + TW);
     EVX_CUDA(cudaFuncSetAttribute(k_dominance_tiles<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
