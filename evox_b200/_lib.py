@@ -53,6 +53,7 @@ _SIGNATURES = {
     "evx_nds_shard_peer_init": (ctypes.c_int, [c_vp, c_vp, c_vp]),
     "evx_nds_shard_peel_fused": (ctypes.c_int, [c_vp, ctypes.POINTER(c_vp), ctypes.POINTER(c_i32), c_vp]),
     "evx_debug_peel_times": (ctypes.c_int, [c_vp, ctypes.POINTER(ctypes.c_uint64)]),
+    "evx_debug_peel_cta_times": (ctypes.c_int, [c_vp, ctypes.POINTER(ctypes.c_uint64), c_i32]),
     "evx_launch_count": (c_i64, []),
     "evx_launch_count_reset": (None, []),
     "evx_profile_enable": (None, [c_i32]),

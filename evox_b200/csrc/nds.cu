@@ -83,7 +83,7 @@ struct Layout {
     int64_t n, npad;
     int m, world, rank, np, npl, npl_max;
     size_t keys, idxA, idxB, skeyA, skeyB, flags, incl, cubtmp, cubtmp_bytes, ucols, row2u, count,
-        rank_u, flist, flist2, cplanes, mask, scal, bits, total, tcols, label, partials, pdone, pcnt, ptab;
+        rank_u, flist, flist2, cplanes, mask, scal, bits, total, tcols, label, partials, pdone, pcnt, ptab, ctadbg;
     int kplanes;
     int64_t bits_words;
 };
@@ -153,6 +153,7 @@ static Layout make_layout(int64_t n, int m, int world, int rank) {
     L.partials = take(sizeof(uint32_t) * (size_t)(PEEL_MAX_GRID + L.npl_max / 2 + 1) * PEEL_KMAX * 64);
     L.pcnt = take(sizeof(uint64_t) * 2 * (size_t)(L.np + 2));          // per-panel front sizes (tagged words), double buffered
     L.pdone = take(sizeof(unsigned int) * 2 * (size_t)L.npl_max);      // arrivals, commits
+    L.ctadbg = take(sizeof(unsigned long long) * 4 * PEEL_MAX_GRID);   // per-CTA phase clocks of the peel (evx_debug_peel_cta_times)
     L.scal = take(sizeof(Scal));
     L.bits_words = pair_words_before(L.npl / 2, world, rank);
     L.bits = take(sizeof(uint32_t) * (size_t)L.bits_words);
@@ -1450,7 +1451,7 @@ template <bool MULTI>
 __global__ void __launch_bounds__(PEEL_WARPS * 32, 2)
 k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count, int* __restrict__ rank_u, FWord* segA,
                FWord* segB, Scal* scal, uint32_t* __restrict__ cplanes, FWord* pcnt, int pstride, uint32_t* partials,
-               unsigned int* pdone, int K, int world, int rank, PeerTable pt) {
+               unsigned int* pdone, int K, int world, int rank, PeerTable pt, unsigned long long* ctadbg) {
     extern __shared__ __align__(128) unsigned char peel_smem_raw[];
     DynShared& sh = *reinterpret_cast<DynShared*>(peel_smem_raw);
     uint32_t (*acc)[PW2] = sh.acc;
@@ -1832,6 +1833,7 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
         }
     }
     if (B == 0 && threadIdx.x == 0) scal->fronts = k;
+    if (threadIdx.x == 0) { ctadbg[4 * B] = t_acc; ctadbg[4 * B + 1] = t_mc; ctadbg[4 * B + 2] = t_bar; ctadbg[4 * B + 3] = t_scan; }
     if (threadIdx.x == 0 && (B == 0 || B == G - 1)) {
         unsigned long long* d = scal->dbg + (B == 0 ? 0 : 4);
         d[0] = t_acc; d[1] = t_mc; d[2] = t_bar; d[3] = (unsigned long long)(k > 0 ? k : 1);
@@ -2058,7 +2060,9 @@ static int peel_persistent(const Plan& P, cudaStream_t s, const PeerTable* peers
         fb = P.at<FWord>(L.flist2);
         EVX_CUDA(cudaMemsetAsync(pcnt, 0, sizeof(FWord) * 2 * (size_t)ps, s));     // epoch 0 = never valid
     }
-    void* args[] = {&bits, &count, &rank_u, &fa, &fb, &scal, &cpl, &pcnt, &ps, &partials, &pdone, &K, &world, &rank, &pt};
+    unsigned long long* ctadbg = P.at<unsigned long long>(L.ctadbg);
+    EVX_CUDA(cudaMemsetAsync(ctadbg, 0, sizeof(unsigned long long) * 4 * PEEL_MAX_GRID, s));
+    void* args[] = {&bits, &count, &rank_u, &fa, &fb, &scal, &cpl, &pcnt, &ps, &partials, &pdone, &K, &world, &rank, &pt, &ctadbg};
     EVX_CUDA(cudaLaunchCooperativeKernel(dk, dim3(dgrid), dim3(PEEL_WARPS * 32), args, dyn_smem, s));
     ++evx::launch_counter();
     return EVX_OK;
@@ -2219,6 +2223,15 @@ extern "C" int evx_debug_peel_times(evx_nds_shard* p, uint64_t* out8) {
     }
     Scal* scal = p->P.at<Scal>(p->P.L.scal);
     EVX_CUDA(cudaMemcpy(out8, scal->dbg, sizeof(uint64_t) * 16, cudaMemcpyDeviceToHost));
+    return EVX_OK;
+}
+
+// Per-CTA phase clocks of the plan's last peel: out[4 * b + {0,1,2,3}] = ns CTA b spent gathering, in merge +
+// commit + publish, waiting for the next front, in the scans (zero for CTAs that did not exist).
+extern "C" int evx_debug_peel_cta_times(evx_nds_shard* p, uint64_t* out, int32_t max_ctas) {
+    EVX_REQUIRE(p && out && max_ctas > 0, EVX_ERR_ARG, "evx_debug_peel_cta_times: bad argument");
+    const int nb = max_ctas < PEEL_MAX_GRID ? max_ctas : PEEL_MAX_GRID;
+    EVX_CUDA(cudaMemcpy(out, p->P.at<unsigned long long>(p->P.L.ctadbg), sizeof(uint64_t) * 4 * nb, cudaMemcpyDeviceToHost));
     return EVX_OK;
 }
 

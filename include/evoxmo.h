@@ -239,6 +239,9 @@ int evx_profile_last(float* prep_ms, float* tiles_ms, float* peel_ms);
  * said "complete", and the time of the two scans that follow (first / last CTA).  p == NULL: the values of this host thread's
  * last evx_nds_f32 call made with evx_profile_enable(1).                                            */
 int evx_debug_peel_times(evx_nds_shard* p, uint64_t* out16);
+/* the same four clocks for every CTA of the plan's last (fused or single-rank shard) peel: out[4*b + {0,1,2,3}] =
+ * ns gathering, merge + commit + publish, waiting, scans; max_ctas <= 1024 entries are written.     */
+int evx_debug_peel_cta_times(evx_nds_shard* p, uint64_t* out, int32_t max_ctas);
 #ifdef __cplusplus
 }
 #endif
