@@ -75,7 +75,7 @@ struct Scal {
     int any[ANY_SLOTS];
     int fronts;     // persistent peel: number of fronts found (-1: a peer timed out)
     unsigned int arrived;   // persistent peel, one GPU: panels published so far in this launch (see PeerState::arrived)
-    unsigned int ctas_done; // fused multi-rank peel: CTA arrivals at the end of a front, all fronts of this launch
+    unsigned int pad0;
     unsigned long long dbg[16];  // persistent peel: ns spent by CTA 0 / last CTA in accumulate, merge+commit, waiting (see evx_debug_peel_times)
 };
 
@@ -1369,11 +1369,12 @@ __device__ __forceinline__ void peel_commit_seg(uint32_t* cp, int K, Delta delta
 // that covers every warp's planes, ranks and members), then tell every rank how many panels this CTA
 // has published for the coming front.
 // `call` = how many times this CTA has been here in this launch (1 = after the init).  Fused multi-rank:
-// every CTA adds its panels to the LOCAL counter; the CTA that arrives last on this GPU stores the
-// front's epoch into the rank's slot on every peer.
+// every CTA adds its panels to the LOCAL counter; the CTA whose panels complete the front on this GPU
+// (counter = abase + nlocal * call) stores the front's epoch into the rank's slot on every peer.
 template <bool MULTI>
 __device__ __forceinline__ void publish_pending(PubList* pub, FWord* cnt_next, unsigned int fe_next, Scal* scal,
-                                                const PeerTable& pt, unsigned int call, unsigned int nlocal) {
+                                                const PeerTable& pt, unsigned int call, unsigned int nlocal,
+                                                unsigned int abase) {
     __syncthreads();                                  // every warp's commits are issued
     if (threadIdx.x == 0) {
         const int n = pub->n, listed = n < PUB_CAP ? n : PUB_CAP;
@@ -1383,15 +1384,17 @@ __device__ __forceinline__ void publish_pending(PubList* pub, FWord* cnt_next, u
         pub->n = 0;                                   // (the next commits are several CTA barriers away)
         pub->extra = 0;
         if constexpr (MULTI) {
-            if (total)
-                asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(&peer_state(pt, pt.rank)->arrived), "r"(total) : "memory");
-            if (pt.world > 1) {
+            if (total && pt.world > 1) {
+                // the CTA whose panels complete the front on this GPU tells the peers (the counter only moves on
+                // to the next front after every rank has seen this one complete)
                 unsigned int old;
-                asm volatile("atom.relaxed.gpu.global.add.u32 %0, [%1], 1;" : "=r"(old) : "l"(&scal->ctas_done) : "memory");
-                if (old + 1u == call * gridDim.x)                          // last CTA of this GPU to finish the front
+                asm volatile("atom.relaxed.gpu.global.add.u32 %0, [%1], %2;" : "=r"(old) : "l"(&peer_state(pt, pt.rank)->arrived), "r"(total) : "memory");
+                if (old + total == abase + nlocal * call)
                     for (int r = 0; r < pt.world; ++r)
                         if (r != pt.rank)
                             asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(&peer_state(pt, r)->done_epoch[pt.rank]), "r"(fe_next) : "memory");
+            } else if (total) {
+                asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(&peer_state(pt, pt.rank)->arrived), "r"(total) : "memory");
             }
         } else {
             if (total) asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(&scal->arrived), "r"(total) : "memory");
@@ -1420,6 +1423,10 @@ constexpr int PEEL_WARP_PAIR_GROUPS = EVX_WPG;    // a pair with at most this ma
 // Fixed cost of visiting a pair, in units of one group's gather time (~0.4 us for a CTA): a pair done by
 // one warp costs its CTA about one unit (eight of them run side by side), a pair done by the whole CTA
 // pays for the merge tree, the commit and four CTA-wide barriers.
+#ifndef EVX_WIDE
+#define EVX_WIDE 3
+#endif
+constexpr int PEEL_WIDE_PARTS = EVX_WIDE;         // from this many CTAs sharing a pair on, their sums are added by all warps
 constexpr int PEEL_COST_WARP_PAIR = EVX_CW;
 constexpr int PEEL_COST_CTA_PAIR = EVX_CC;
 static_assert(PEEL_WARP_PAIR_GROUPS + PEEL_COST_WARP_PAIR < 1 + PEEL_COST_CTA_PAIR, "the two kinds must be told apart by total cost");
@@ -1445,6 +1452,24 @@ __device__ __forceinline__ void store_planes(uint32_t (*m)[PW2], const Planes& p
     for (int p = 0; p < PEEL_UP; ++p)
         if (3 + p < pm) { m[3 + p][lane] = pa.up[p]; m[3 + p][PW + lane] = pb.up[p]; }
     for (int p = PEEL_RP; p < pm; ++p) { m[p][lane] = 0u; m[p][PW + lane] = 0u; }
+}
+
+// Sum the eight warps' plane sets (planes [0, pm)) into sh.merge[0]: three levels, warps [0, half) take
+// panel 0's words and warps [half, 2*half) panel 1's.  Called by the whole CTA, after a barrier.
+__device__ __forceinline__ void merge_tree(uint32_t (*merge)[PEEL_PM][PW2], int pm, int warp, int lane) {
+    for (int half = PEEL_WARPS / 2; half >= 1; half >>= 1) {
+        if (warp < 2 * half) {
+            const int wl = warp % half, off = (warp / half) * PW + lane;
+            uint32_t carry = 0;
+            for (int p = 0; p < pm; ++p) {
+                const uint32_t a = merge[wl][p][off], b2 = merge[wl + half][p][off];
+                const uint32_t x = a ^ b2;
+                merge[wl][p][off] = x ^ carry;
+                carry = (a & b2) | (x & carry);
+            }
+        }
+        __syncthreads();
+    }
 }
 
 template <bool MULTI>
@@ -1509,7 +1534,7 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
             }
             __syncthreads();
         }
-        publish_pending<MULTI>(&sh.pub, cnt0, e0, scal, pt, 1u, nlocal);
+        publish_pending<MULTI>(&sh.pub, cnt0, e0, scal, pt, 1u, nlocal, abase);
     }
 
     Ring2 rg;
@@ -1744,19 +1769,7 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
                     store_planes(sh.merge[warp], pa, pb, pm, lane);
                     __syncthreads();
                     if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_acc += t - t_mark; t_mark = t; }
-                    for (int half = PEEL_WARPS / 2; half >= 1; half >>= 1) {
-                        if (warp < 2 * half) {
-                            const int wl = warp % half, off = (warp / half) * PW + lane;
-                            uint32_t carry = 0;
-                            for (int p = 0; p < pm; ++p) {
-                                const uint32_t a = sh.merge[wl][p][off], b2 = sh.merge[wl + half][p][off];
-                                const uint32_t x = a ^ b2;
-                                sh.merge[wl][p][off] = x ^ carry;
-                                carry = (a & b2) | (x & carry);
-                            }
-                        }
-                        __syncthreads();
-                    }
+                    merge_tree(sh.merge, pm, warp, lane);
                     pm_last = pm;
                     if (direct) break;
                     if (warp < 2) {                                 // acc += this pass (warp h: panel h)
@@ -1771,7 +1784,7 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
                     }
                     __syncthreads();
                 }
-                bool commit = true;
+                bool commit = true, wide = false;
                 if (parts > 1) {
                     // Shared pair: park this CTA's sums (slot lp + B is unique per front), count
                     // arrivals; the last one adds the others' sums to its own and commits.
@@ -1782,13 +1795,55 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
                         __threadfence();
                         const unsigned int old = atomicAdd(&pdone[lp], 1u);
                         const bool last = old + 1u == (unsigned int)parts;
-                        if (last) pdone[lp] = 0u;
+                        if (last) {
+                            pdone[lp] = 0u;
+                            __threadfence();                        // acquire: the others' parked sums
+                        }
                         sh.nf = last ? 1 : 0;
-                        __threadfence();
                     }
                     __syncthreads();
                     commit = sh.nf != 0;
-                    if (commit && warp < 2) {
+                    wide = commit && parts >= PEEL_WIDE_PARTS && pq <= PEEL_PM;
+                    if (wide) {
+                        // Many parts: the L2 round trips of a serial sum would line up on the front's critical
+                        // path.  Warp w sums parts w, w + 8, ... (this CTA's own from shared memory), the merge
+                        // tree adds the eight results: one round trip for up to eight parts.
+                        uint32_t sa[PEEL_PM], sb[PEEL_PM];
+#pragma unroll
+                        for (int p = 0; p < PEEL_PM; ++p) { sa[p] = 0u; sb[p] = 0u; }
+                        for (int i = warp; i < parts; i += PEEL_WARPS) {
+                            const int b2 = (T >= G) ? bf + i : owner(g0 + i);
+                            uint32_t oa[PEEL_PM], ob[PEEL_PM];
+                            if (b2 == B) {
+#pragma unroll
+                                for (int p = 0; p < PEEL_PM; ++p) {
+                                    oa[p] = (p < pq) ? acc[p][lane] : 0u;
+                                    ob[p] = (p < pq) ? acc[p][PW + lane] : 0u;
+                                }
+                            } else {
+                                const uint32_t* other = partials + (size_t)(lp + b2) * PEEL_KMAX * PW2 + lane;
+#pragma unroll
+                                for (int p = 0; p < PEEL_PM; ++p) {
+                                    oa[p] = (p < pq) ? __ldcg(other + p * PW2) : 0u;
+                                    ob[p] = (p < pq) ? __ldcg(other + p * PW2 + PW) : 0u;
+                                }
+                            }
+                            uint32_t ca = 0, cb = 0;
+#pragma unroll
+                            for (int p = 0; p < PEEL_PM; ++p) {
+                                const uint32_t xa = sa[p] ^ oa[p], xb = sb[p] ^ ob[p];
+                                const uint32_t na = (sa[p] & oa[p]) | (xa & ca), nb = (sb[p] & ob[p]) | (xb & cb);
+                                sa[p] = xa ^ ca; sb[p] = xb ^ cb;
+                                ca = na; cb = nb;
+                            }
+                        }
+#pragma unroll
+                        for (int p = 0; p < PEEL_PM; ++p)
+                            if (p < pq) { sh.merge[warp][p][lane] = sa[p]; sh.merge[warp][p][PW + lane] = sb[p]; }
+                        __syncthreads();
+                        merge_tree(sh.merge, pq, warp, lane);       // the pair's total is below 2^pq: no carry out
+                    }
+                    if (commit && !wide && warp < 2) {
                         const int off = warp * PW + lane;
                         for (int i = 0; i < parts; ++i) {
                             const int b2 = (T >= G) ? bf + i : owner(g0 + i);
@@ -1814,7 +1869,7 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
                     const int J = 2 * Q + warp, l = 2 * lp + warp;
                     if (J < npan)
                         peel_commit_seg<MULTI>(cplanes + (size_t)l * cp_stride, K,
-                                               SmemDelta{direct ? &sh.merge[0][0][warp * PW + lane] : &acc[0][warp * PW + lane]},
+                                               SmemDelta{direct || wide ? &sh.merge[0][0][warp * PW + lane] : &acc[0][warp * PW + lane]},
                                                direct ? pm_last : pq, lane, J, seg_next, cnt_next, fe + 1u,
                                                rank_u + (size_t)l * TW, k + 1, pt, &sh.pub);
                 }
@@ -1822,7 +1877,7 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
                 if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_mc += t - t_mark; t_mark = t; }
             }
         }
-        publish_pending<MULTI>(&sh.pub, cnt_next, fe + 1u, scal, pt, (unsigned int)k + 2u, nlocal);
+        publish_pending<MULTI>(&sh.pub, cnt_next, fe + 1u, scal, pt, (unsigned int)k + 2u, nlocal, abase);
         if (threadIdx.x == 0) { const unsigned long long t = global_ns(); t_mc += t - t_mark; t_mark = t; }
     }
     if constexpr (MULTI) {
