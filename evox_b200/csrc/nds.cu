@@ -1559,7 +1559,7 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
             bool done = false;
             if (warp == 0) {                                        // hints: my GPU's panels of fronts 0..k, and every peer done with front k
                 const unsigned int target = abase + nlocal * (unsigned int)(k + 1);
-                const bool peer = MULTI && lane < pt.world && lane != pt.rank;
+                const bool peer = MULTI && lane < pt.world && lane != pt.rank && lane < nqg;   // ranks >= nqg own no live panel and send nothing
                 const unsigned int* word = peer ? &peer_state(pt, pt.rank)->done_epoch[lane] : arrived;
                 const unsigned int want = peer ? fe : target;
                 for (unsigned int spin = 0;; ++spin) {
