@@ -18,8 +18,8 @@ from ._lib import EvoxMoError, check, lib
 def recommended_world(n, available=8):
     """How many GPUs to give one non-dominated sort of n rows (measured on 8 x B200, profiles/r2_scaling.md):
     the bit matrix shrinks as 1/G but every front costs one exchange across all GPUs, so small populations
-    with many light fronts are fastest on one GPU (N = 200k: 3.50 ms on one, 3.55 on two, 4.57 on eight),
-    while N = 1M gains up to eight (31.2 -> 10.4 ms)."""
+    with many light fronts gain next to nothing (N = 200k: 3.24 ms on one, 3.09 on two, 3.07 on four, 3.28 on
+    eight), while N = 1M gains up to eight (28.7 -> 9.1 ms)."""
     if n < 300_000:
         want = 1
     elif n < 500_000:
