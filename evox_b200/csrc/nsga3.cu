@@ -5,12 +5,16 @@
 // the one-survivor-per-iteration `while_loop`, up to pop_size sequential steps, each of which touches
 // several arrays of N elements in the reference).  The normalisation before it (:103-139: ideal point,
 // extreme points, a tiny M x M solve) stays host glue.
-//   associate - one thread per solution, reference directions staged in shared memory already divided
-//               by their norm; nothing N x R is stored.
+//   associate - a thread takes up to four solutions, reference directions are staged in shared memory already
+//               divided by their norm; nothing N x R is stored.  The distance is monotone in 1 - c^2, so the
+//               square root is only taken when a direction improves on the best so far.
 //   niche     - the last front's members are sorted by (group, index) once (radix sort); one persistent
-//               CTA then runs the loop: arg-min of the niche counts through per-thread chunk minima (only
-//               the chunk of the group that changed is rescanned), the candidate by smallest distance or
-//               by the caller's random words with jax.random.randint's own arithmetic, updates.
+//               CTA then runs the reference's loop LEVEL BY LEVEL instead of pick by pick: the loop always
+//               serves the first niche with the smallest count, so all niches at the smallest count c are
+//               served in index order before any niche at c + 1 - within a level the picks are independent,
+//               and the loop index of each (which selects its random words) is its position in the level.
+//               One step per level: minimum, flags, one scan, then every thread makes the picks of its own
+//               niches; a niche with many candidates left is served by the whole CTA.
 // The random words are an INPUT (two 32-bit words per loop index, what randint(keys[i], ...) consumes),
 // so the host framework's PRNG stream stays the reference's.
 #include <cub/device/device_radix_sort.cuh>
@@ -62,6 +66,83 @@ k_nsga3_associate(const float* __restrict__ x, const float* __restrict__ ref, in
     if (i < n) { gid[i] = bi; gdist[i] = best; }
 }
 
+// The same for a compile-time number of objectives: RPT solutions per thread (each staged direction is read
+// once for all of them), FMA dot product, and d = |x| sqrt(1 - c^2) only when 1 - c^2 is below the best
+// direction's (sqrt and the product are monotone under round-to-nearest, so a direction with a larger or
+// equal 1 - c^2 can never be strictly closer: the first minimum is unchanged).
+template <int M, int RPT>
+__global__ void __launch_bounds__(AS_T)
+k_nsga3_associate_t(const float* __restrict__ x, const float* __restrict__ ref, int n, int R, int* __restrict__ gid,
+                    float* __restrict__ gdist) {
+    extern __shared__ float tile[];                   // [AS_TILE][M]
+    float xn[RPT][M], nx[RPT], best[RPT], best_s[RPT];
+    int bi[RPT];
+#pragma unroll
+    for (int r = 0; r < RPT; ++r) {
+        const int i = (blockIdx.x * RPT + r) * AS_T + threadIdx.x;
+        nx[r] = 0.0f;
+        best[r] = __int_as_float(0x7FC00000);         // NaN until a number is seen
+        best_s[r] = INFINITY;
+        bi[r] = R;
+        if (i < n) {
+            float acc = 0.0f;
+#pragma unroll
+            for (int k = 0; k < M; ++k) { xn[r][k] = x[(size_t)i * M + k]; acc = __fadd_rn(acc, __fmul_rn(xn[r][k], xn[r][k])); }
+            nx[r] = __fsqrt_rn(acc);
+#pragma unroll
+            for (int k = 0; k < M; ++k) xn[r][k] = __fdiv_rn(xn[r][k], nx[r]);
+        } else {
+#pragma unroll
+            for (int k = 0; k < M; ++k) xn[r][k] = __int_as_float(0x7FC00000);      // never improves
+        }
+    }
+    for (int r0 = 0; r0 < R; r0 += AS_TILE) {
+        const int nt = min(AS_TILE, R - r0);
+        __syncthreads();
+        for (int t = threadIdx.x; t < nt; t += AS_T) {
+            const float* y = ref + (size_t)(r0 + t) * M;
+            float acc = 0.0f;
+#pragma unroll
+            for (int k = 0; k < M; ++k) acc = __fadd_rn(acc, __fmul_rn(y[k], y[k]));
+            const float ny = __fsqrt_rn(acc);
+#pragma unroll
+            for (int k = 0; k < M; ++k) tile[t * M + k] = __fdiv_rn(y[k], ny);
+        }
+        __syncthreads();
+        for (int t = 0; t < nt; ++t) {
+            float y[M];
+#pragma unroll
+            for (int k = 0; k < M; ++k) y[k] = tile[t * M + k];
+#pragma unroll
+            for (int r = 0; r < RPT; ++r) {
+                float c = __fmul_rn(xn[r][0], y[0]);
+#pragma unroll
+                for (int k = 1; k < M; ++k) c = __fmaf_rn(xn[r][k], y[k], c);
+                const float sq = __fmaf_rn(-c, c, 1.0f);
+                if (sq < best_s[r]) {                                           // false for NaN
+                    const float d = __fmul_rn(nx[r], __fsqrt_rn(sq));
+                    if (d == d && !(best[r] <= d)) { best[r] = d; best_s[r] = sq; bi[r] = r0 + t; }
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < RPT; ++r) {
+        const int i = (blockIdx.x * RPT + r) * AS_T + threadIdx.x;
+        if (i < n) { gid[i] = bi[r]; gdist[i] = best[r]; }
+    }
+}
+
+template <int M>
+static void launch_associate_t(const float* x, const float* ref, int n, int R, int* gid, float* gd, cudaStream_t s) {
+    constexpr int RPT = M <= 12 ? 4 : 2;
+    // small populations: fewer rows per thread so that the grid still covers the chip
+    if ((int64_t)n >= (int64_t)148 * 4 * AS_T * RPT)
+        k_nsga3_associate_t<M, RPT><<<(unsigned)ceil_div(n, AS_T * RPT), AS_T, sizeof(float) * AS_TILE * M, s>>>(x, ref, n, R, gid, gd);
+    else
+        k_nsga3_associate_t<M, 1><<<(unsigned)ceil_div(n, AS_T), AS_T, sizeof(float) * AS_TILE * M, s>>>(x, ref, n, R, gid, gd);
+}
+
 // ---- niching ------------------------------------------------------------------------------------------
 struct NicheScal { int selected; };
 
@@ -80,17 +161,19 @@ __global__ void k_niche_counts(const int* __restrict__ rank, const int* __restri
 }
 
 constexpr int NI_T = 1024;
+constexpr int NI_HEAVY = 64;          // a niche with more candidates left than this is served by the whole CTA
 constexpr int RHO_INF = 0x7FFFFFFF;
 
-// One CTA.  cand[] = last-front members sorted by (group, index); off[g] = first entry of group g.
+// One CTA.  cand[] = last-front members sorted by (group, index); off[g] = first entry of group g;
+// heavy[] = (niche, loop index) of the level's picks that are left to the whole CTA.
 __global__ void __launch_bounds__(NI_T)
 k_niche_loop(int* __restrict__ rank, const float* __restrict__ gdist, const int* __restrict__ cand, int n, int R,
              int last_rank, int pop_size, int* __restrict__ rho, int* __restrict__ rho_last, int* __restrict__ off,
              uint8_t* __restrict__ taken, const uint32_t* __restrict__ rbits, int* __restrict__ selected_idx,
-             int* __restrict__ nsel_out) {
-    __shared__ int cmin[NI_T], cidx[NI_T];            // per-chunk minimum of rho and its first index
-    __shared__ int wv[32], wi[32];
-    __shared__ int s_sel, s_group;
+             int* __restrict__ nsel_out, int* __restrict__ heavy) {
+    __shared__ int wv[32], wi[32], wc[32];
+    __shared__ float wf[32];
+    __shared__ int s_sel, s_nheavy;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int chunk = (R + NI_T - 1) / NI_T;
     // offsets (exclusive scan of rho_last), selected = sum(rho), rho = inf where the group has no candidate (:158-160)
@@ -116,78 +199,162 @@ k_niche_loop(int* __restrict__ rank, const float* __restrict__ gdist, const int*
             run += rho_last[g];
             if (rho_last[g] == 0) rho[g] = RHO_INF;
         }
+        if (t * chunk < R && min(R, (t + 1) * chunk) == R) off[R] = run;    // end of the last group's entries
         __syncthreads();
     }
-    auto rescan = [&](int th) {                       // chunk minimum of thread th's groups (first index on ties)
-        int bv = RHO_INF, bi = 0x7FFFFFFF;
-        for (int g = th * chunk; g < min(R, (th + 1) * chunk); ++g)
-            if (rho[g] < bv) { bv = rho[g]; bi = g; }
-        if (bi == 0x7FFFFFFF && th * chunk < R) bi = th * chunk;            // all inf: first index of the chunk
-        cmin[th] = bv; cidx[th] = bi;
+    // jax.random.randint(key, (), 0, span) from the two words it consumes (oracle/jax_prng.randint_from_bits)
+    auto draw = [&](int loop_index, int left) -> int {
+        const uint32_t span = (uint32_t)left;
+        const uint32_t hi = rbits[2 * loop_index], lo = rbits[2 * loop_index + 1];
+        uint32_t mult = (65536u % span) * (65536u % span);
+        mult %= span;
+        uint32_t offv = (hi % span) * mult + (lo % span);
+        return (int)(offv % span);
     };
-    rescan(t);
-    __syncthreads();
-    int selected = s_sel;
-    while (selected < pop_size) {                                           // :196-200
-        // group = argmin(rho), first index (:169)
-        int bv = cmin[t], bi = cidx[t];
-#pragma unroll
-        for (int o = 16; o >= 1; o >>= 1) {
-            const int ov = __shfl_xor_sync(0xFFFFFFFFu, bv, o), oi = __shfl_xor_sync(0xFFFFFFFFu, bi, o);
-            if (ov < bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+    auto retire = [&](int group, int level, int pick, int left) {
+        taken[pick] = 1;
+        rank[cand[pick]] = last_rank - 1;                                   // :189
+        rho_last[group] = left - 1;                                         // :191
+        rho[group] = (left - 1 == 0) ? RHO_INF : level + 1;                 // :193-201
+    };
+    // One pick by the thread that owns the niche (few candidates left).  The group's entries are
+    // cand[off[group] ..) in index order; taken ones are skipped.
+    auto light_pick = [&](int group, int level, int loop_index) {
+        const int first = off[group];
+        const int left = rho_last[group];
+        int pick = -1;
+        if (level == 0 || left == 1) {                                      // :187: closest remaining candidate
+            float bd = INFINITY;
+            int seen = 0;
+            for (int q = first; seen < left; ++q) {
+                if (taken[q]) continue;
+                ++seen;
+                const float d = gdist[cand[q]];
+                if (pick < 0 || d < bd) { bd = d; pick = q; }               // ascending index: first minimum
+            }
+        } else {                                                            // :173-183: the rand_index-th remaining, by index
+            const int offv = draw(loop_index, left);
+            int seen = 0;
+            for (int q = first;; ++q) {
+                if (taken[q]) continue;
+                if (seen == offv) { pick = q; break; }
+                ++seen;
+            }
         }
-        if (lane == 0) { wv[warp] = bv; wi[warp] = bi; }
-        __syncthreads();
-        if (warp == 0) {
-            bv = wv[lane]; bi = wi[lane];
+        retire(group, level, pick, left);
+    };
+    // The same pick by the whole CTA, for a niche with many candidates left: thread t looks at a contiguous
+    // piece of the group's entries.
+    auto heavy_pick = [&](int group, int level, int loop_index) {
+        const int first = off[group], len = off[group + 1] - first, left = rho_last[group];
+        const int per = (len + NI_T - 1) / NI_T;
+        const int q0 = first + min(len, t * per), q1 = first + min(len, (t + 1) * per);
+        if (level == 0) {
+            float bd = INFINITY;
+            int bq = 0x7FFFFFFF;
+            for (int q = q0; q < q1; ++q) {
+                if (taken[q]) continue;
+                const float d = gdist[cand[q]];
+                if (bq == 0x7FFFFFFF || d < bd) { bd = d; bq = q; }
+            }
 #pragma unroll
             for (int o = 16; o >= 1; o >>= 1) {
-                const int ov = __shfl_xor_sync(0xFFFFFFFFu, bv, o), oi = __shfl_xor_sync(0xFFFFFFFFu, bi, o);
-                if (ov < bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+                const float od = __shfl_xor_sync(0xFFFFFFFFu, bd, o);
+                const int oq = __shfl_xor_sync(0xFFFFFFFFu, bq, o);
+                if (oq != 0x7FFFFFFF && (bq == 0x7FFFFFFF || od < bd || (od == bd && oq < bq))) { bd = od; bq = oq; }
             }
-            if (lane == 0) s_group = (bv == RHO_INF) ? -1 : bi;     // -1: no candidate anywhere (cannot happen for pop_size < n)
+            if (lane == 0) { wf[warp] = bd; wi[warp] = bq; }
+            __syncthreads();
+            if (warp == 0) {
+                bd = wf[lane]; bq = wi[lane];
+#pragma unroll
+                for (int o = 16; o >= 1; o >>= 1) {
+                    const float od = __shfl_xor_sync(0xFFFFFFFFu, bd, o);
+                    const int oq = __shfl_xor_sync(0xFFFFFFFFu, bq, o);
+                    if (oq != 0x7FFFFFFF && (bq == 0x7FFFFFFF || od < bd || (od == bd && oq < bq))) { bd = od; bq = oq; }
+                }
+                if (lane == 0) retire(group, level, bq, left);
+            }
+        } else {
+            const int offv = draw(loop_index, left);
+            int c = 0;
+            for (int q = q0; q < q1; ++q) c += taken[q] ? 0 : 1;
+            int incl = c;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+                if (lane >= o) incl += v;
+            }
+            if (lane == 31) wi[warp] = incl;
+            __syncthreads();
+            int before = incl - c;
+            for (int w = 0; w < warp; ++w) before += wi[w];
+            if (before <= offv && offv < before + c) {                     // exactly one thread
+                int seen = before;
+                for (int q = q0; q < q1; ++q) {
+                    if (taken[q]) continue;
+                    if (seen == offv) { retire(group, level, q, left); break; }
+                    ++seen;
+                }
+            }
         }
         __syncthreads();
-        const int group = s_group;
-        if (group < 0) break;
-        if (t == 0) {
-            const int first = off[group];
-            const int left = rho_last[group];
-            // the group's entries: cand[first .. first + initial count); find that count lazily while scanning
-            int pick = -1;
-            if (rho[group] == 0 || left == 1) {                             // :187: closest remaining candidate
-                float bd = INFINITY;
-                int seen = 0;
-                for (int q = first; seen < left; ++q) {
-                    if (taken[q]) continue;
-                    ++seen;
-                    const float d = gdist[cand[q]];
-                    if (pick < 0 || d < bd) { bd = d; pick = q; }           // ascending index: first minimum
-                }
-            } else {                                                        // :173-183: the rand_index-th remaining, by index
-                const uint32_t span = (uint32_t)left;
-                const uint32_t hi = rbits[2 * selected], lo = rbits[2 * selected + 1];
-                uint32_t mult = (65536u % span) * (65536u % span);
-                mult %= span;
-                uint32_t offv = (hi % span) * mult + (lo % span);
-                offv %= span;
-                int seen = 0;
-                for (int q = first;; ++q) {
-                    if (taken[q]) continue;
-                    if (seen == (int)offv) { pick = q; break; }
-                    ++seen;
+    };
+
+    const int g_lo = min(R, t * chunk), g_hi = min(R, (t + 1) * chunk);    // this thread's niches
+    int selected = s_sel;
+    while (selected < pop_size) {                                           // :196-200, one level per turn
+        // the smallest count: every niche that has it is served once, in index order (:169 takes the first)
+        int bv = RHO_INF;
+        for (int g = g_lo; g < g_hi; ++g) bv = min(bv, rho[g]);
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) bv = min(bv, __shfl_xor_sync(0xFFFFFFFFu, bv, o));
+        if (lane == 0) wv[warp] = bv;
+        if (t == 0) s_nheavy = 0;
+        __syncthreads();
+        int level = wv[lane];
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) level = min(level, __shfl_xor_sync(0xFFFFFFFFu, level, o));
+        if (level == RHO_INF) break;                                        // no candidate anywhere (cannot happen for pop_size < n)
+        int cnt = 0;
+        for (int g = g_lo; g < g_hi; ++g) cnt += (rho[g] == level) ? 1 : 0;
+        int incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane == 31) wc[warp] = incl;
+        __syncthreads();
+        int before = incl - cnt, total = 0;
+        for (int w = 0; w < 32; ++w) {
+            const int v = wc[w];
+            if (w < warp) before += v;
+            total += v;
+        }
+        // the niche at position p of the level is loop index selected + p (its random words); positions
+        // past pop_size are never reached by the reference's loop
+        int p = selected + before;
+        for (int g = g_lo; g < g_hi; ++g) {
+            if (rho[g] != level) continue;
+            if (p < pop_size) {
+                if (rho_last[g] > NI_HEAVY) {
+                    const int slot = atomicAdd(&s_nheavy, 1);
+                    heavy[2 * slot] = g;
+                    heavy[2 * slot + 1] = p;
+                } else {
+                    light_pick(g, level, p);
                 }
             }
-            taken[pick] = 1;
-            rank[cand[pick]] = last_rank - 1;                               // :189
-            rho_last[group] = left - 1;                                     // :191
-            rho[group] = (left - 1 == 0) ? RHO_INF : rho[group] + 1;        // :193-201
+            ++p;
         }
         __syncthreads();
-        if (t == group / chunk) rescan(t);
-        ++selected;
+        const int nh = s_nheavy;
+        for (int h = 0; h < nh; ++h) heavy_pick(heavy[2 * h], level, heavy[2 * h + 1]);
+        selected += min(total, pop_size - selected);
         __syncthreads();
     }
+    __syncthreads();
     // survivors: rank < last_rank, ascending index, first pop_size (:202-204)
     __shared__ int base;
     if (t == 0) base = 0;
@@ -210,7 +377,7 @@ k_niche_loop(int* __restrict__ rank, const float* __restrict__ gdist, const int*
 }
 
 struct NicheLayout {
-    size_t rank, rho, rho_last, off, keysA, keysB, valsA, valsB, taken, tmp, tmp_bytes, total;
+    size_t rank, rho, rho_last, off, heavy, keysA, keysB, valsA, valsB, taken, tmp, tmp_bytes, total;
 };
 static NicheLayout niche_layout(int64_t n, int64_t R) {
     NicheLayout L{};
@@ -220,6 +387,7 @@ static NicheLayout niche_layout(int64_t n, int64_t R) {
     L.rho = take(sizeof(int) * (size_t)(R + 1));
     L.rho_last = take(sizeof(int) * (size_t)(R + 1));
     L.off = take(sizeof(int) * (size_t)(R + 1));
+    L.heavy = take(sizeof(int) * 2 * (size_t)(R + 1));
     L.keysA = take(sizeof(uint32_t) * (size_t)n);
     L.keysB = take(sizeof(uint32_t) * (size_t)n);
     L.valsA = take(sizeof(int) * (size_t)n);
@@ -242,8 +410,17 @@ extern "C" int evx_nsga3_associate_f32(const float* normalized, const float* ref
                 "evx_nsga3_associate_f32: bad shape n=%lld nref=%lld m=%d", (long long)n, (long long)nref, m);
     if (n == 0) return EVX_OK;
     EVX_REQUIRE(normalized && ref && group_id && group_dist, EVX_ERR_ARG, "evx_nsga3_associate_f32: null pointer");
-    k_nsga3_associate<<<(unsigned)ceil_div(n, AS_T), AS_T, sizeof(float) * AS_TILE * m, (cudaStream_t)stream>>>(
-        normalized, ref, (int)n, (int)nref, m, group_id, group_dist);
+    cudaStream_t s = (cudaStream_t)stream;
+    switch (m) {
+#define EVX_ASSOC_CASE(MM) case MM: launch_associate_t<MM>(normalized, ref, (int)n, (int)nref, group_id, group_dist, s); break;
+        EVX_ASSOC_CASE(2) EVX_ASSOC_CASE(3) EVX_ASSOC_CASE(4) EVX_ASSOC_CASE(5) EVX_ASSOC_CASE(6) EVX_ASSOC_CASE(7) EVX_ASSOC_CASE(8)
+        EVX_ASSOC_CASE(9) EVX_ASSOC_CASE(10) EVX_ASSOC_CASE(11) EVX_ASSOC_CASE(12) EVX_ASSOC_CASE(13) EVX_ASSOC_CASE(14)
+        EVX_ASSOC_CASE(15) EVX_ASSOC_CASE(16)
+#undef EVX_ASSOC_CASE
+        default:
+            k_nsga3_associate<<<(unsigned)ceil_div(n, AS_T), AS_T, sizeof(float) * AS_TILE * m, s>>>(normalized, ref, (int)n, (int)nref, m,
+                                                                                               group_id, group_dist);
+    }
     EVX_LAUNCH_CHECK();
     return EVX_OK;
 }
@@ -268,6 +445,7 @@ extern "C" int evx_nsga3_niche(const int32_t* rank, int32_t last_rank, const int
     int* rho = reinterpret_cast<int*>(base + L.rho);
     int* rho_last = reinterpret_cast<int*>(base + L.rho_last);
     int* off = reinterpret_cast<int*>(base + L.off);
+    int* heavy = reinterpret_cast<int*>(base + L.heavy);
     uint32_t* kA = reinterpret_cast<uint32_t*>(base + L.keysA);
     uint32_t* kB = reinterpret_cast<uint32_t*>(base + L.keysB);
     int* vA = reinterpret_cast<int*>(base + L.valsA);
@@ -284,7 +462,7 @@ extern "C" int evx_nsga3_niche(const int32_t* rank, int32_t last_rank, const int
     size_t tb = L.tmp_bytes;
     EVX_CUDA(cub::DeviceRadixSort::SortPairs(base + L.tmp, tb, kA, kB, vA, vB, (int)n, 0, bits, s));
     k_niche_loop<<<1, NI_T, 0, s>>>(rk, group_dist, vB, (int)n, (int)nref, last_rank, (int)pop_size, rho, rho_last, off, taken,
-                                    rand_words, selected_idx, nullptr);
+                                    rand_words, selected_idx, nullptr, heavy);
     EVX_LAUNCH_CHECK();
     return EVX_OK;
 }

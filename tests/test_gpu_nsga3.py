@@ -53,7 +53,10 @@ def test_associate_and_niche_on_fixture_cases(i):
     assert (pop[aux["selected"]] == G[f"n3_{i}_opop"]).all() and (fit[aux["selected"]] == G[f"n3_{i}_ofit"]).all()
 
 
-@pytest.mark.parametrize("n,m,nref,ps", [(4000, 3, 91, 2000), (3000, 5, 210, 1500), (2000, 10, 275, 1000), (1000, 2, 1000, 500)])
+@pytest.mark.parametrize("n,m,nref,ps", [(4000, 3, 91, 2000), (3000, 5, 210, 1500), (2000, 10, 275, 1000), (1000, 2, 1000, 500),
+                                         # niches with more than 64 candidates (served by the whole CTA): random picks,
+                                         # then (last front = front 0, every count 0) closest-candidate picks as well
+                                         (4000, 3, 5, 2000), (3000, 3, 2, 1500), (2000, 3, 3, 200), (6000, 4, 1, 2500)])
 def test_niche_larger_vs_oracle(n, m, nref, ps):
     """Random but consistent inputs at sizes of a few thousand: ranks with a last front that must be cut,
     random group assignments and distances (with ties), random draw words."""
