@@ -51,7 +51,10 @@ def test_cal_fitness_vs_oracle(n, m, kind):
 
 
 @pytest.mark.parametrize("n,m,k,p,kind", [(1500, 3, 700, 0.9, "random"), (800, 2, 300, 0.5, "ties"), (400, 3, 399, 1.0, "random"),
-                                          (600, 4, 0, 0.7, "random"), (500, 3, 200, 1.0, "dupes")])
+                                          (600, 4, 0, 0.7, "random"), (500, 3, 200, 1.0, "dupes"),
+                                          # neighbour lists that run out (clusters of identical points, heavy removal)
+                                          (900, 3, 600, 1.0, "clusters"), (1800, 3, 1000, 0.9, "random"),
+                                          (700, 7, 650, 1.0, "random"), (600, 2, 400, 0.8, "clusters")])
 def test_truncation_vs_oracle(n, m, k, p, kind):
     from oracle import oracle_np as O
     from evox_b200.algorithms.spea2 import _truncation
@@ -61,6 +64,8 @@ def test_truncation_vs_oracle(n, m, k, p, kind):
         obj = rng.integers(0, 20, (n, m)).astype(np.float32)        # many equal distances: index order decides
     elif kind == "dupes":
         obj[::3] = obj[1::3][: len(obj[::3])]
+    elif kind == "clusters":
+        obj = obj[rng.integers(0, 20, n)]                            # 20 distinct points, ~n / 20 copies of each
     mask = rng.random(n) < p
     k = min(k, max(0, int(mask.sum()) - 1))
     want = O.spea2_truncation(obj, k, mask)
