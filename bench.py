@@ -372,6 +372,7 @@ def run_ours(args):
         if not args.no_nsga2:
             line["nsga2"] = nsga2_gens_per_s(torch)
             line["nsga2_small"] = nsga2_gens_per_s(torch, pop=100, d=7, m=3, gens=100, problem="DTLZ1")   # configs[0] shape
+            line["nsga2_mid"] = nsga2_gens_per_s(torch, pop=2500, d=12, m=3, gens=100, problem="DTLZ2")    # merged N = 5000: one-CTA peel
         line["operators"] = operator_rates(torch, hbm_peak)
         line["other_inputs"] = other_inputs(torch, L, n, m, args)
     if not args.no_cpu_baseline:
@@ -431,6 +432,33 @@ def operator_rates(torch, hbm_peak):
         b = 4.0 * nn * (d + mm)
         out[f"evaluate_{name}"] = {"workload": f"n={nn} d={d} m={mm}", "evals_per_s": nn / t, "GB/s": b / t / 1e9,
                                    "frac_of_hbm_peak": b / t / 1e9 / hbm_peak, "us": t * 1e6}
+    # NSGA-III environmental selection at the configs[3] shape (MaF1-like: merged n = 100k, M = 10,
+    # 48 620 reference directions = Das-Dennis H = 9)
+    from evox_b200.algorithms import nsga3, spea2
+    n, m, R, ps = 100_000, 10, 48_620, 50_000
+    fit = torch.rand((n, m), device="cuda", generator=g)
+    ref = torch.rand((R, m), device="cuda", generator=g) + 0.01
+    rank = E.operators.non_dominated_sort(fit)
+    last_rank = int(rank[torch.sort(rank, stable=True).indices[ps]])
+    norm = nsga3.normalize(fit, rank, last_rank)
+    gid, gd = nsga3.associate(norm, ref)
+    rw = torch.randint(0, 2**31 - 1, (ps + 1, 2), device="cuda", dtype=torch.int32, generator=g)
+    pop = torch.rand((n, 19), device="cuda", generator=g)
+    ta = med(lambda: nsga3.associate(norm, ref), reps=5, inner=2)
+    tn = med(lambda: nsga3.niche(rank, last_rank, gid, gd, R, ps, rw), reps=5, inner=2)
+    te = med(lambda: nsga3.environmental_selection(pop, fit, ref, ps, rw), reps=5, inner=1)
+    out["nsga3_selection"] = {"workload": f"merged n={n} M={m} refs={R} pop={ps}", "associate_ms": ta * 1e3,
+                              "associate_pairs_per_s": n * R / ta, "niche_ms": tn * 1e3,
+                              "niche_picks": ps - int((rank < last_rank).sum()), "whole_selection_ms": te * 1e3}
+    # SPEA2 fitness assignment and archive truncation (merged n = 20k, M = 3, 60 % valid cut to 50 %)
+    n, m = 20_000, 3
+    obj = torch.rand((n, m), device="cuda", generator=g)
+    mask = torch.rand(n, device="cuda", generator=g) < 0.6
+    k = int(mask.sum()) - n // 2
+    tf = med(lambda: spea2.cal_fitness(obj), reps=5, inner=2)
+    tt = med(lambda: spea2._truncation(obj, k, mask), reps=3, inner=1)
+    out["spea2"] = {"workload": f"n={n} M={m}, truncation removes {k} rows", "cal_fitness_ms": tf * 1e3,
+                    "cal_fitness_pairs_per_s": float(n) * n / tf, "truncation_ms": tt * 1e3}
     return out
 
 

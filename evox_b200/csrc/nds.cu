@@ -1897,6 +1897,224 @@ k_peel_dynamic(const uint32_t* __restrict__ bits, const int* __restrict__ count,
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Small populations (at most PS_MAX_PAN panels, N <= 8192) on one GPU: ONE CTA peels all fronts.
+// The persistent kernel above pays about 12 us per front in flags, fences and polling between its CTAs
+// whatever the front's size; here a front costs three CTA barriers and a scan.  Count planes, alive
+// masks and the front list (row indices, ascending) live in shared memory.
+// The 32 warps are dealt to the pairs, W = 32, 16 or 8 each, and inside a pair as RS row shares x 8
+// column shares: a warp covers 8 of the super-row's 64 words (32 bytes = one sector), its lanes are
+// 8 row slots x 4 lanes of 8 bytes, so one load instruction fetches full sectors of eight different
+// rows and a lane always sees the same two columns' words.  A lane counts its rows (at most 127 per
+// pass) in carry-save counters, the eight row slots are added up with shuffles - no shared memory, no
+// barrier - and slot 0's lanes add the result to the pair's sums.  After one barrier the same lanes
+// subtract the sums from the panel's planes; the zero columns - the next front - are appended in row
+// order by a scan over the new-member words.
+// ------------------------------------------------------------------------------------------------
+constexpr int PS_T = 1024, PS_WARPS = PS_T / 32;
+constexpr int PS_MAX_PAN = 8;                     // N <= 8192: above, the multi-CTA kernel's bandwidth wins (measured)
+constexpr int PS_MAX_PAIRS = PS_MAX_PAN / 2;
+constexpr int PS_K = 14;                          // count planes: counts < 2^14 > 8192
+constexpr int PS_CS = 8;                          // column shares of a pair: 8 words each
+constexpr int PS_LANE_ROWS = 127;                 // rows per lane and pass: 7 counter planes
+constexpr int PS_MP = 10;                         // planes after adding the 8 row slots: 8 * 127 < 2^10
+struct SingleShared {
+    uint32_t planes[PS_MAX_PAN][PS_K + 1][PW];      // [.][PS_K] = alive mask
+    uint32_t acc[PS_MAX_PAIRS][PS_K][PW2];          // sums over the front's rows: [pair * RS + row share] (pairs * RS <= 4)
+    uint32_t neww[PS_MAX_PAN * PW];                 // new members, one word per 32 columns
+    uint16_t list[2][PS_MAX_PAN * TW];              // the front (row indices, ascending), double buffered
+    int pre[PS_MAX_PAN + 1];                        // members in panels < J
+    int wsum[PS_WARPS];
+};
+
+// eight more rows into carry-save counters c[0..6] (ones .. sixty-fours): at most 127 rows in all
+__device__ __forceinline__ void csa8_small(uint32_t (&c)[PS_MP], const uint32_t* x) {
+    uint32_t ta, tb, fa, fb, e;
+    csa(ta, c[0], c[0], x[0], x[1]);
+    csa(tb, c[0], c[0], x[2], x[3]);
+    csa(fa, c[1], c[1], ta, tb);
+    csa(ta, c[0], c[0], x[4], x[5]);
+    csa(tb, c[0], c[0], x[6], x[7]);
+    csa(fb, c[1], c[1], ta, tb);
+    csa(e, c[2], c[2], fa, fb);
+#pragma unroll
+    for (int p = 3; p < 7; ++p) {
+        const uint32_t carry = c[p] & e;
+        c[p] ^= e;
+        e = carry;
+    }
+}
+
+__global__ void __launch_bounds__(PS_T, 1)
+k_peel_single(const uint32_t* __restrict__ bits, const int* __restrict__ count, int* __restrict__ rank_u, Scal* scal) {
+    extern __shared__ __align__(128) unsigned char ps_smem_raw[];
+    SingleShared& sh = *reinterpret_cast<SingleShared*>(ps_smem_raw);
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int U = scal->U;
+    const int npan = (U + TW - 1) / TW;
+    const int nq = (npan + 1) / 2;
+    int K = 1;
+    while ((1 << K) <= U) ++K;                      // counts are below U
+    // ---- init: int counts -> planes, alive masks ------------------------------------------------------
+    for (int w = warp; w < npan * PW; w += PS_WARPS) {
+        const int J = w / PW, wc = w % PW;
+        const int j = J * TW + wc * 32 + lane;
+        const int v = (j < U) ? count[(size_t)J * TW + wc * 32 + lane] : 0;
+        for (int p = 0; p < K; ++p) {
+            const uint32_t b = __ballot_sync(0xFFFFFFFFu, (v >> p) & 1);
+            if (lane == 0) sh.planes[J][p][wc] = b;
+        }
+        const uint32_t a = __ballot_sync(0xFFFFFFFFu, j < U);
+        const uint32_t z = __ballot_sync(0xFFFFFFFFu, j < U && v == 0);
+        if (lane == 0) {
+            sh.planes[J][PS_K][wc] = a & ~z;
+            sh.neww[w] = z;                         // front 0
+        }
+    }
+    __syncthreads();
+    // new-member words -> list (ascending rows), members per panel, ranks; returns the front's size
+    auto emit = [&](uint16_t* list, int front) -> int {
+        const int words = npan * PW;                // <= 256
+        const uint32_t w = t < words ? sh.neww[t] : 0u;
+        const int c = __popc(w);
+        int incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane == 31) sh.wsum[warp] = incl;
+        __syncthreads();
+        int before = incl - c, total = 0;
+        for (int q = 0; q < PS_WARPS; ++q) {
+            const int v = sh.wsum[q];
+            if (q < warp) before += v;
+            total += v;
+        }
+        if (t < words && (t % PW) == 0) sh.pre[t / PW] = before;
+        if (t == 0) sh.pre[npan] = total;
+        uint32_t x = w;
+        while (x) {
+            const int b = __ffs(x) - 1;
+            x &= x - 1;
+            const int row = t * 32 + b;             // word t covers columns [32 t, 32 t + 32)
+            list[before++] = (uint16_t)row;
+            rank_u[row] = front;
+        }
+        __syncthreads();                            // list and pre complete, wsum free again
+        return total;
+    };
+    uint16_t* cur = sh.list[0];
+    uint16_t* nxt = sh.list[1];
+    int nf = emit(cur, 0);
+    // warps per pair, and the warp's place: pair, row share, column share; lane: row slot, 8-byte piece
+    const int W = nq <= 1 ? 32 : nq == 2 ? 16 : 8;
+    const int RS = W / PS_CS;
+    const int grp = warp / W, wl = warp % W;
+    const int rs = wl / PS_CS, cs = wl % PS_CS;
+    const int slot = lane >> 2, q = lane & 3;
+    const bool live = grp < nq;
+    const int word0 = cs * 8 + 2 * q;               // this lane's two words of the super-row: word0, word0 + 1
+    const int J = 2 * grp + (word0 >> 5), wp = word0 & 31;    // their panel and place in it
+    const uint32_t* pbase = bits + pair_words_before(live ? grp : 0, 1, 0) + word0;
+    uint32_t* accw = &sh.acc[live ? grp * RS + rs : 0][0][word0];
+    const int stride = 8 * RS;                      // list positions between a lane's rows
+    int k = 0;
+    while (nf > 0) {
+        ++k;
+        // rows pair Q needs: the members in panels < 2Q + 2, a prefix of the ascending list
+        const int rows = live ? sh.pre[min(2 * grp + 2, npan)] : 0;
+        const int passes = (nf + stride * PS_LANE_ROWS - 1) / (stride * PS_LANE_ROWS);   // pair nq - 1 sees every member
+        if (live && slot == 0)
+            for (int p = 0; p < K; ++p) { accw[p * PW2] = 0u; accw[p * PW2 + 1] = 0u; }
+        for (int pass = 0; pass < passes; ++pass) {
+            const int base = pass * stride * PS_LANE_ROWS;
+            if (!live || rows <= base) continue;    // (warp-uniform)
+            // ---- gather: list positions base + rs * 8 + slot + stride * u ----
+            uint32_t ca[PS_MP], cb[PS_MP];
+#pragma unroll
+            for (int p = 0; p < PS_MP; ++p) { ca[p] = 0u; cb[p] = 0u; }
+            const int most = min(PS_LANE_ROWS, (rows - base + stride - 1) / stride);    // rows of the pass's first lane
+            const int first = base + rs * 8 + slot;
+            for (int u0 = 0; u0 < most; u0 += 8) {
+                uint32_t xa[8], xb[8];
+#pragma unroll
+                for (int r = 0; r < 8; ++r) {
+                    const int pos = first + (u0 + r) * stride;
+                    uint2 v = make_uint2(0u, 0u);
+                    if (u0 + r < most && pos < rows)
+                        v = __ldcg(reinterpret_cast<const uint2*>(pbase + (size_t)cur[pos] * PW2));
+                    xa[r] = v.x; xb[r] = v.y;
+                }
+                csa8_small(ca, xa);
+                csa8_small(cb, xb);
+            }
+            // ---- the eight row slots: bit-sliced adds across lanes 4, 8, 16 apart ----
+#pragma unroll
+            for (int m = 4; m <= 16; m <<= 1) {
+                uint32_t cya = 0, cyb = 0;
+#pragma unroll
+                for (int p = 0; p < PS_MP; ++p) {
+                    const uint32_t oa = __shfl_xor_sync(0xFFFFFFFFu, ca[p], m), ob = __shfl_xor_sync(0xFFFFFFFFu, cb[p], m);
+                    const uint32_t sa = ca[p] ^ oa, sb = cb[p] ^ ob;
+                    const uint32_t na = (ca[p] & oa) | (sa & cya), nb = (cb[p] & ob) | (sb & cyb);
+                    ca[p] = sa ^ cya; cb[p] = sb ^ cyb;
+                    cya = na; cyb = nb;
+                }
+            }
+            // ---- into the sums of this row share (slot 0's lanes own their two words) ----
+            if (slot == 0) {
+                uint32_t cya = 0, cyb = 0;
+#pragma unroll
+                for (int p = 0; p < PS_K; ++p) {
+                    if (p < K) {
+                        const uint32_t a = accw[p * PW2], b = accw[p * PW2 + 1];
+                        const uint32_t da = p < PS_MP ? ca[p] : 0u, db = p < PS_MP ? cb[p] : 0u;
+                        const uint32_t sa = a ^ da, sb = b ^ db;
+                        accw[p * PW2] = sa ^ cya; accw[p * PW2 + 1] = sb ^ cyb;
+                        cya = (a & da) | (sa & cya); cyb = (b & db) | (sb & cyb);
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        // ---- row shares together, subtract, retire the zero columns: slot 0's lanes of row share 0 ----
+        if (live && rs == 0 && slot == 0 && J < npan) {
+            uint32_t nwa = 0u, nwb = 0u;
+            if (rows > 0) {
+                for (int o = 1; o < RS; ++o) {
+                    const uint32_t* other = &sh.acc[grp * RS + o][0][word0];
+                    uint32_t cya = 0, cyb = 0;
+                    for (int p = 0; p < K; ++p) {
+                        const uint32_t a = accw[p * PW2], b = accw[p * PW2 + 1], da = other[p * PW2], db = other[p * PW2 + 1];
+                        const uint32_t sa = a ^ da, sb = b ^ db;
+                        accw[p * PW2] = sa ^ cya; accw[p * PW2 + 1] = sb ^ cyb;
+                        cya = (a & da) | (sa & cya); cyb = (b & db) | (sb & cyb);
+                    }
+                }
+                uint32_t bwa = 0, bwb = 0, nza = 0, nzb = 0;
+                for (int p = 0; p < K; ++p) {
+                    const uint32_t c0 = sh.planes[J][p][wp], c1 = sh.planes[J][p][wp + 1];
+                    const uint32_t d0 = accw[p * PW2], d1 = accw[p * PW2 + 1];
+                    const uint32_t x0 = c0 ^ d0, x1 = c1 ^ d1;
+                    const uint32_t r0 = x0 ^ bwa, r1 = x1 ^ bwb;
+                    bwa = (~c0 & d0) | (~x0 & bwa); bwb = (~c1 & d1) | (~x1 & bwb);
+                    sh.planes[J][p][wp] = r0; sh.planes[J][p][wp + 1] = r1;
+                    nza |= r0; nzb |= r1;
+                }
+                const uint32_t al0 = sh.planes[J][PS_K][wp], al1 = sh.planes[J][PS_K][wp + 1];
+                nwa = al0 & ~nza; nwb = al1 & ~nzb;
+                sh.planes[J][PS_K][wp] = al0 & ~nwa; sh.planes[J][PS_K][wp + 1] = al1 & ~nwb;
+            }
+            sh.neww[J * PW + wp] = nwa; sh.neww[J * PW + wp + 1] = nwb;
+        }
+        __syncthreads();
+        nf = emit(nxt, k);
+        uint16_t* tmp = cur; cur = nxt; nxt = tmp;
+    }
+    if (t == 0) scal->fronts = k;                  // front k was the first empty one
+}
+
 __global__ void k_write_ranks(const int* __restrict__ row2u, const int* __restrict__ rank_u, int64_t n, int world,
                               int rank, int* __restrict__ out) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -2070,12 +2288,26 @@ static bool persistent_peel_fits(const Layout& L) {
            (L.np + 1) / 2 <= DYN_MAX_PPT * PEEL_WARPS * 32;
 }
 
+static bool force_dynamic_peel() {                                 // EVX_PEEL=dynamic: the multi-CTA kernel at every size
+    const char* e = getenv("EVX_PEEL");
+    return e && strcmp(e, "dynamic") == 0;
+}
+
 // Launch the persistent peel.  peers == nullptr: single rank.  Otherwise the fused multi-rank kernel
 // with the peer buffers.  Leaves the front count in scal->fronts (-1 after a time-out).
 static int peel_persistent(const Plan& P, cudaStream_t s, const PeerTable* peers = nullptr) {
     const Layout& L = P.L;
     EVX_REQUIRE(persistent_peel_fits(L), EVX_ERR_ARG, "persistent peel: population of %lld rows exceeds the kernel's tables",
                 (long long)L.n);
+    if (!peers && L.world == 1 && L.np <= PS_MAX_PAN && !force_dynamic_peel()) {
+        // small population on one GPU: one CTA, no flags between CTAs (k_peel_single)
+        EVX_CUDA(cudaFuncSetAttribute(k_peel_single, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SingleShared)));
+        k_peel_single<<<1, PS_T, sizeof(SingleShared), s>>>(P.at<uint32_t>(L.bits), P.at<int>(L.count), P.at<int>(L.rank_u),
+                                                           P.at<Scal>(L.scal));
+        EVX_LAUNCH_CHECK();
+        ++evx::launch_counter();
+        return EVX_OK;
+    }
     int dev = 0, sms = 0, per_sm = 0;
     EVX_CUDA(cudaGetDevice(&dev));
     EVX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
