@@ -214,6 +214,101 @@ __global__ void k_scatter_unique(const float* __restrict__ x, const int* __restr
     if (p == nvalid - 1) scal->U = u + 1;
 }
 
+// ---- small populations: sort + unique in ONE launch ----------------------------------------------------
+// Up to PREP_SMALL_MAX_N rows the M stable radix sorts cost 7 launches each and every onesweep pass
+// ~10 us of latency on a handful of tiles (12 of them at M = 3: 0.13 ms at N = 6000, a quarter of the
+// whole sort).  Here one CTA holds all keys in shared memory and bitonic-sorts the row indices by
+// (key_0, .., key_{M-1}, index) - a total order, so the result is the stable lexicographic order the
+// radix passes give - then marks the heads of runs of equal keys, scans, and scatters the unique rows
+// (k_mark_heads + InclusiveSum + k_scatter_unique).
+constexpr int PREP_SMALL_MAX_N = 8192;
+constexpr int PREP_SMALL_MAX_M = 6;               // keys of 8192 rows x 6 objectives = 192 KB of shared memory
+constexpr int SU_T = 1024, SU_ITEMS = PREP_SMALL_MAX_N / SU_T;
+
+__global__ void __launch_bounds__(SU_T, 1)
+k_small_sort_unique(const float* __restrict__ x, const uint32_t* __restrict__ keys, int n, int m, int64_t npad, Scal* scal,
+                    float* __restrict__ tcols, int* __restrict__ row2u) {
+    extern __shared__ uint32_t ss_smem[];             // [m][n] keys, then P row indices (uint16)
+    __shared__ int wsum[SU_T / 32];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    int P = 1;
+    while (P < n) P <<= 1;                            // sorted length: rows + sentinels (index >= n: after every row)
+    uint32_t* ks = ss_smem;
+    uint16_t* idx = reinterpret_cast<uint16_t*>(ss_smem + (size_t)m * n);
+    for (int i = t; i < m * n; i += SU_T) ks[i] = keys[i];
+    for (int i = t; i < P; i += SU_T) idx[i] = (uint16_t)i;
+    __syncthreads();
+    auto before = [&](int a, int b) -> bool {         // does row a come before row b?
+        if (a >= n || b >= n) return a < b;
+        for (int k = 0; k < m; ++k) {
+            const uint32_t ka = ks[k * n + a], kb = ks[k * n + b];
+            if (ka != kb) return ka < kb;
+        }
+        return a < b;
+    };
+    for (int k = 2; k <= P; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int q = t; q < (P >> 1); q += SU_T) {
+                const int i = ((q & ~(j - 1)) << 1) | (q & (j - 1));      // q-th index with bit j clear
+                const int a = idx[i], b = idx[i | j];
+                const bool up = (i & k) == 0;
+                if (before(b, a) == up) { idx[i] = (uint16_t)b; idx[i | j] = (uint16_t)a; }
+            }
+            __syncthreads();
+        }
+    }
+    // ---- heads of runs, scan, unique rows out ----------------------------------------------------------
+    const int nvalid = n - scal->n_nan;
+    int cnt = 0;
+    uint32_t heads = 0;
+#pragma unroll
+    for (int e = 0; e < SU_ITEMS; ++e) {
+        const int p = t * SU_ITEMS + e;
+        int head = 0;
+        if (p < nvalid) {
+            if (p == 0) head = 1;
+            else {
+                const int a = idx[p], b = idx[p - 1];
+                for (int k = 0; k < m; ++k) head |= (ks[k * n + a] != ks[k * n + b]) ? 1 : 0;
+            }
+        }
+        heads |= (uint32_t)head << e;
+        cnt += head;
+    }
+    int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    int run = incl - cnt, total = 0;
+    for (int w = 0; w < SU_T / 32; ++w) {
+        const int v = wsum[w];
+        if (w < warp) run += v;
+        total += v;
+    }
+#pragma unroll
+    for (int e = 0; e < SU_ITEMS; ++e) {
+        const int p = t * SU_ITEMS + e;
+        if (p < n) {
+            const int row = idx[p];
+            if (p >= nvalid) {
+                row2u[row] = -1;
+            } else {
+                const int head = (heads >> e) & 1;
+                run += head;
+                const int u = run - 1;
+                row2u[row] = u;
+                if (head)
+                    for (int k = 0; k < m; ++k) tcols[(size_t)k * npad + u] = x[(size_t)row * m + k] + 0.0f;
+            }
+        }
+    }
+    if (t == 0) scal->U = total;
+}
+
 // ------------------------------------------------------------------------------------------------
 // stage 1b: block-local re-labelling
 // ------------------------------------------------------------------------------------------------
@@ -2172,6 +2267,11 @@ static int launch_tiles(const Plan& P, cudaStream_t s) {
     return EVX_OK;
 }
 
+static bool force_radix_prep() {                                   // EVX_PREP=radix: the radix-sort path at every size
+    const char* e = getenv("EVX_PREP");
+    return e && strcmp(e, "radix") == 0;
+}
+
 static int build(const Plan& P, const float* x, cudaStream_t s, cudaEvent_t tiles_begin = nullptr,
                  cudaEvent_t tiles_end = nullptr) {
     const Layout& L = P.L;
@@ -2190,21 +2290,30 @@ static int build(const Plan& P, const float* x, cudaStream_t s, cudaEvent_t tile
     int* idx_nxt = P.at<int>(L.idxB);
     k_make_keys<<<gn, T, 0, s>>>(x, n, m, keys, idx_cur, scal);
     EVX_LAUNCH_CHECK();
-    for (int k = m - 1; k >= 0; --k) {            // LSD passes of a stable sort = lexicographic order
-        k_gather_key<<<gn, T, 0, s>>>(keys + (int64_t)k * n, idx_cur, n, P.at<uint32_t>(L.skeyA));
+    if (n <= PREP_SMALL_MAX_N && m <= PREP_SMALL_MAX_M && !force_radix_prep()) {
+        int pw2 = 1;
+        while (pw2 < n) pw2 <<= 1;
+        const size_t sm = sizeof(uint32_t) * (size_t)m * n + sizeof(uint16_t) * (size_t)pw2;
+        EVX_CUDA(cudaFuncSetAttribute(k_small_sort_unique, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+        k_small_sort_unique<<<1, SU_T, sm, s>>>(x, keys, (int)n, m, L.npad, scal, P.at<float>(L.tcols), P.at<int>(L.row2u));
+        EVX_LAUNCH_CHECK();
+    } else {
+        for (int k = m - 1; k >= 0; --k) {            // LSD passes of a stable sort = lexicographic order
+            k_gather_key<<<gn, T, 0, s>>>(keys + (int64_t)k * n, idx_cur, n, P.at<uint32_t>(L.skeyA));
+            EVX_LAUNCH_CHECK();
+            size_t tb = L.cubtmp_bytes;
+            EVX_CUDA(cub::DeviceRadixSort::SortPairs(P.at<void>(L.cubtmp), tb, P.at<uint32_t>(L.skeyA),
+                                                     P.at<uint32_t>(L.skeyB), idx_cur, idx_nxt, (int)n, 0, 32, s));
+            int* t = idx_cur; idx_cur = idx_nxt; idx_nxt = t;
+        }
+        k_mark_heads<<<gn, T, 0, s>>>(keys, idx_cur, n, m, scal, P.at<int>(L.flags));
         EVX_LAUNCH_CHECK();
         size_t tb = L.cubtmp_bytes;
-        EVX_CUDA(cub::DeviceRadixSort::SortPairs(P.at<void>(L.cubtmp), tb, P.at<uint32_t>(L.skeyA),
-                                                 P.at<uint32_t>(L.skeyB), idx_cur, idx_nxt, (int)n, 0, 32, s));
-        int* t = idx_cur; idx_cur = idx_nxt; idx_nxt = t;
+        EVX_CUDA(cub::DeviceScan::InclusiveSum(P.at<void>(L.cubtmp), tb, P.at<int>(L.flags), P.at<int>(L.incl), (int)n, s));
+        k_scatter_unique<<<gn, T, 0, s>>>(x, idx_cur, P.at<int>(L.incl), P.at<int>(L.flags), n, m, L.npad, scal,
+                                          P.at<float>(L.tcols), P.at<int>(L.row2u));
+        EVX_LAUNCH_CHECK();
     }
-    k_mark_heads<<<gn, T, 0, s>>>(keys, idx_cur, n, m, scal, P.at<int>(L.flags));
-    EVX_LAUNCH_CHECK();
-    size_t tb = L.cubtmp_bytes;
-    EVX_CUDA(cub::DeviceScan::InclusiveSum(P.at<void>(L.cubtmp), tb, P.at<int>(L.flags), P.at<int>(L.incl), (int)n, s));
-    k_scatter_unique<<<gn, T, 0, s>>>(x, idx_cur, P.at<int>(L.incl), P.at<int>(L.flags), n, m, L.npad, scal,
-                                      P.at<float>(L.tcols), P.at<int>(L.row2u));
-    EVX_LAUNCH_CHECK();
     // labels: block-local f1 order, word-local f2 order (one CTA per block)
     k_block_labels<<<(unsigned)L.np, TW, 0, s>>>(P.at<float>(L.tcols), L.npad, m, scal, P.at<float>(L.ucols),
                                                  P.at<int>(L.label));
