@@ -161,19 +161,19 @@ __global__ void k_niche_counts(const int* __restrict__ rank, const int* __restri
 }
 
 constexpr int NI_T = 1024;
-constexpr int NI_HEAVY = 64;          // a niche with more candidates left than this is served by the whole CTA
+constexpr int NI_HEAVY = 64;          // a niche with more entries than this is served by a warp, not by its owner thread
 constexpr int RHO_INF = 0x7FFFFFFF;
 
 // One CTA.  cand[] = last-front members sorted by (group, index); off[g] = first entry of group g;
-// heavy[] = (niche, loop index) of the level's picks that are left to the whole CTA.
+// taken = one bit per entry; live[] = the niches that have candidates; heavy[] = (niche, loop index) of
+// the level's picks that are left to a warp each.
 __global__ void __launch_bounds__(NI_T)
 k_niche_loop(int* __restrict__ rank, const float* __restrict__ gdist, const int* __restrict__ cand, int n, int R,
              int last_rank, int pop_size, int* __restrict__ rho, int* __restrict__ rho_last, int* __restrict__ off,
-             uint8_t* __restrict__ taken, const uint32_t* __restrict__ rbits, int* __restrict__ selected_idx,
-             int* __restrict__ nsel_out, int* __restrict__ heavy) {
+             uint32_t* taken, const uint32_t* __restrict__ rbits, int* __restrict__ selected_idx,
+             int* __restrict__ nsel_out, int* __restrict__ heavy, int* __restrict__ live) {
     __shared__ int wv[32], wi[32], wc[32];
-    __shared__ float wf[32];
-    __shared__ int s_sel, s_nheavy;
+    __shared__ int s_sel, s_nheavy, s_nlive;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int chunk = (R + NI_T - 1) / NI_T;
     // offsets (exclusive scan of rho_last), selected = sum(rho), rho = inf where the group has no candidate (:158-160)
@@ -202,6 +202,28 @@ k_niche_loop(int* __restrict__ rank, const float* __restrict__ gdist, const int*
         if (t * chunk < R && min(R, (t + 1) * chunk) == R) off[R] = run;    // end of the last group's entries
         __syncthreads();
     }
+    // ---- the niches that have candidates, ascending, compact: thread t owns live[t * lchunk ..) ------------
+    {
+        int c = 0;
+        for (int g = t * chunk; g < min(R, (t + 1) * chunk); ++g) c += rho_last[g] > 0 ? 1 : 0;
+        int incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane == 31) wv[warp] = incl;
+        __syncthreads();
+        int run = incl - c, tot = 0;
+        for (int w = 0; w < 32; ++w) { if (w < warp) run += wv[w]; tot += wv[w]; }
+        for (int g = t * chunk; g < min(R, (t + 1) * chunk); ++g)
+            if (rho_last[g] > 0) live[run++] = g;
+        if (t == 0) s_nlive = tot;
+        __syncthreads();
+    }
+    const int nlive = s_nlive;
+    const int lchunk = (nlive + NI_T - 1) / NI_T;
+    const int l_lo = min(nlive, t * lchunk), l_hi = min(nlive, (t + 1) * lchunk);
     // jax.random.randint(key, (), 0, span) from the two words it consumes (oracle/jax_prng.randint_from_bits)
     auto draw = [&](int loop_index, int left) -> int {
         const uint32_t span = (uint32_t)left;
@@ -211,51 +233,65 @@ k_niche_loop(int* __restrict__ rank, const float* __restrict__ gdist, const int*
         uint32_t offv = (hi % span) * mult + (lo % span);
         return (int)(offv % span);
     };
+    // The group's entries are cand[off[g] .. off[g + 1]) in index order; bit q of `taken` = entry q is gone.
+    // Remaining entries of word w that belong to [first, end):
+    auto avail = [&](int w, int first, int end) -> uint32_t {
+        uint32_t m = ~__ldcg(&taken[w]);                                     // (bits are set by atomics: read them where those land)
+        const int lo = w * 32;
+        if (first > lo) m &= 0xFFFFFFFFu << (first - lo);
+        if (end < lo + 32) m &= (end <= lo) ? 0u : (0xFFFFFFFFu >> (lo + 32 - end));
+        return m;
+    };
     auto retire = [&](int group, int level, int pick, int left) {
-        taken[pick] = 1;
+        atomicOr(&taken[pick >> 5], 1u << (pick & 31));                     // neighbouring groups share boundary words
         rank[cand[pick]] = last_rank - 1;                                   // :189
         rho_last[group] = left - 1;                                         // :191
         rho[group] = (left - 1 == 0) ? RHO_INF : level + 1;                 // :193-201
     };
-    // One pick by the thread that owns the niche (few candidates left).  The group's entries are
-    // cand[off[group] ..) in index order; taken ones are skipped.
+    // One pick by ONE thread (group with at most NI_HEAVY entries: three words at most).
     auto light_pick = [&](int group, int level, int loop_index) {
-        const int first = off[group];
+        const int first = off[group], end = off[group + 1];
         const int left = rho_last[group];
         int pick = -1;
-        if (level == 0 || left == 1) {                                      // :187: closest remaining candidate
+        if (level == 0 && left > 1) {                                       // :187: closest remaining candidate
             float bd = INFINITY;
-            int seen = 0;
-            for (int q = first; seen < left; ++q) {
-                if (taken[q]) continue;
-                ++seen;
-                const float d = gdist[cand[q]];
-                if (pick < 0 || d < bd) { bd = d; pick = q; }               // ascending index: first minimum
+            for (int w = first >> 5; w <= (end - 1) >> 5; ++w) {
+                uint32_t m = avail(w, first, end);
+                while (m) {
+                    const int q = w * 32 + __ffs(m) - 1;
+                    m &= m - 1;
+                    const float d = gdist[cand[q]];
+                    if (pick < 0 || d < bd) { bd = d; pick = q; }           // ascending index: first minimum
+                }
             }
         } else {                                                            // :173-183: the rand_index-th remaining, by index
-            const int offv = draw(loop_index, left);
-            int seen = 0;
-            for (int q = first;; ++q) {
-                if (taken[q]) continue;
-                if (seen == offv) { pick = q; break; }
-                ++seen;
+            int k = left == 1 ? 0 : draw(loop_index, left);                 // (one left: it is also the closest)
+            for (int w = first >> 5; w <= (end - 1) >> 5; ++w) {
+                const uint32_t m = avail(w, first, end);
+                const int c = __popc(m);
+                if (k < c) { pick = w * 32 + (int)__fns(m, 0, k + 1); break; }
+                k -= c;
             }
         }
         retire(group, level, pick, left);
     };
-    // The same pick by the whole CTA, for a niche with many candidates left: thread t looks at a contiguous
-    // piece of the group's entries.
+    // The same pick by ONE WARP, for a group with many entries: lane l takes a contiguous run of words.
     auto heavy_pick = [&](int group, int level, int loop_index) {
-        const int first = off[group], len = off[group + 1] - first, left = rho_last[group];
-        const int per = (len + NI_T - 1) / NI_T;
-        const int q0 = first + min(len, t * per), q1 = first + min(len, (t + 1) * per);
-        if (level == 0) {
+        const int first = off[group], end = off[group + 1], left = rho_last[group];
+        const int w0 = first >> 5, nw = ((end - 1) >> 5) - w0 + 1;
+        const int per = (nw + 31) / 32;
+        const int wa = w0 + min(nw, lane * per), wb = w0 + min(nw, (lane + 1) * per);
+        if (level == 0 && left > 1) {
             float bd = INFINITY;
             int bq = 0x7FFFFFFF;
-            for (int q = q0; q < q1; ++q) {
-                if (taken[q]) continue;
-                const float d = gdist[cand[q]];
-                if (bq == 0x7FFFFFFF || d < bd) { bd = d; bq = q; }
+            for (int w = wa; w < wb; ++w) {
+                uint32_t m = avail(w, first, end);
+                while (m) {
+                    const int q = w * 32 + __ffs(m) - 1;
+                    m &= m - 1;
+                    const float d = gdist[cand[q]];
+                    if (bq == 0x7FFFFFFF || d < bd) { bd = d; bq = q; }
+                }
             }
 #pragma unroll
             for (int o = 16; o >= 1; o >>= 1) {
@@ -263,96 +299,87 @@ k_niche_loop(int* __restrict__ rank, const float* __restrict__ gdist, const int*
                 const int oq = __shfl_xor_sync(0xFFFFFFFFu, bq, o);
                 if (oq != 0x7FFFFFFF && (bq == 0x7FFFFFFF || od < bd || (od == bd && oq < bq))) { bd = od; bq = oq; }
             }
-            if (lane == 0) { wf[warp] = bd; wi[warp] = bq; }
-            __syncthreads();
-            if (warp == 0) {
-                bd = wf[lane]; bq = wi[lane];
-#pragma unroll
-                for (int o = 16; o >= 1; o >>= 1) {
-                    const float od = __shfl_xor_sync(0xFFFFFFFFu, bd, o);
-                    const int oq = __shfl_xor_sync(0xFFFFFFFFu, bq, o);
-                    if (oq != 0x7FFFFFFF && (bq == 0x7FFFFFFF || od < bd || (od == bd && oq < bq))) { bd = od; bq = oq; }
-                }
-                if (lane == 0) retire(group, level, bq, left);
-            }
+            if (lane == 0) retire(group, level, bq, left);
         } else {
-            const int offv = draw(loop_index, left);
+            const int k = left == 1 ? 0 : draw(loop_index, left);
             int c = 0;
-            for (int q = q0; q < q1; ++q) c += taken[q] ? 0 : 1;
+            for (int w = wa; w < wb; ++w) c += __popc(avail(w, first, end));
             int incl = c;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
                 if (lane >= o) incl += v;
             }
-            if (lane == 31) wi[warp] = incl;
-            __syncthreads();
-            int before = incl - c;
-            for (int w = 0; w < warp; ++w) before += wi[w];
-            if (before <= offv && offv < before + c) {                     // exactly one thread
-                int seen = before;
-                for (int q = q0; q < q1; ++q) {
-                    if (taken[q]) continue;
-                    if (seen == offv) { retire(group, level, q, left); break; }
-                    ++seen;
+            int kk = k - (incl - c);
+            if (kk >= 0 && kk < c) {                                        // exactly one lane
+                for (int w = wa; w < wb; ++w) {
+                    const uint32_t m = avail(w, first, end);
+                    const int cw = __popc(m);
+                    if (kk < cw) { retire(group, level, w * 32 + (int)__fns(m, 0, kk + 1), left); break; }
+                    kk -= cw;
                 }
             }
         }
-        __syncthreads();
+        __syncwarp();
     };
 
-    const int g_lo = min(R, t * chunk), g_hi = min(R, (t + 1) * chunk);    // this thread's niches
     int selected = s_sel;
     while (selected < pop_size) {                                           // :196-200, one level per turn
-        // the smallest count: every niche that has it is served once, in index order (:169 takes the first)
-        int bv = RHO_INF;
-        for (int g = g_lo; g < g_hi; ++g) bv = min(bv, rho[g]);
+        // The smallest count: every niche that has it is served once, in index order (:169 takes the first).
+        // One barrier for both the minimum and the positions: per thread (its minimum, how many of its niches
+        // have it), per warp the same, and every thread folds the 32 warp entries.
+        int bv = RHO_INF, cnt = 0;
+        for (int i = l_lo; i < l_hi; ++i) {
+            const int v = rho[live[i]];
+            if (v < bv) { bv = v; cnt = 1; } else if (v == bv && v != RHO_INF) ++cnt;
+        }
+        int wmin = bv;
 #pragma unroll
-        for (int o = 16; o >= 1; o >>= 1) bv = min(bv, __shfl_xor_sync(0xFFFFFFFFu, bv, o));
-        if (lane == 0) wv[warp] = bv;
-        if (t == 0) s_nheavy = 0;
-        __syncthreads();
-        int level = wv[lane];
-#pragma unroll
-        for (int o = 16; o >= 1; o >>= 1) level = min(level, __shfl_xor_sync(0xFFFFFFFFu, level, o));
-        if (level == RHO_INF) break;                                        // no candidate anywhere (cannot happen for pop_size < n)
-        int cnt = 0;
-        for (int g = g_lo; g < g_hi; ++g) cnt += (rho[g] == level) ? 1 : 0;
-        int incl = cnt;
+        for (int o = 16; o >= 1; o >>= 1) wmin = min(wmin, __shfl_xor_sync(0xFFFFFFFFu, wmin, o));
+        const int mine = (bv == wmin && bv != RHO_INF) ? cnt : 0;          // my niches at the warp's minimum
+        int incl = mine;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
             if (lane >= o) incl += v;
         }
-        if (lane == 31) wc[warp] = incl;
+        if (lane == 31) { wv[warp] = wmin; wc[warp] = incl; }
+        if (t == 0) s_nheavy = 0;
         __syncthreads();
-        int before = incl - cnt, total = 0;
+        int level = RHO_INF;
+        for (int w = 0; w < 32; ++w) level = min(level, wv[w]);
+        if (level == RHO_INF) break;                                        // no candidate anywhere (cannot happen for pop_size < n)
+        int before = 0, total = 0;
         for (int w = 0; w < 32; ++w) {
-            const int v = wc[w];
+            const int v = wv[w] == level ? wc[w] : 0;
             if (w < warp) before += v;
             total += v;
         }
+        if (wmin == level) before += incl - mine;
         // the niche at position p of the level is loop index selected + p (its random words); positions
         // past pop_size are never reached by the reference's loop
-        int p = selected + before;
-        for (int g = g_lo; g < g_hi; ++g) {
-            if (rho[g] != level) continue;
-            if (p < pop_size) {
-                if (rho_last[g] > NI_HEAVY) {
-                    const int slot = atomicAdd(&s_nheavy, 1);
-                    heavy[2 * slot] = g;
-                    heavy[2 * slot + 1] = p;
-                } else {
-                    light_pick(g, level, p);
+        if (bv == level) {
+            int p = selected + before;
+            for (int i = l_lo; i < l_hi; ++i) {
+                const int g = live[i];
+                if (rho[g] != level) continue;
+                if (p < pop_size) {
+                    if (off[g + 1] - off[g] > NI_HEAVY) {
+                        const int slot = atomicAdd(&s_nheavy, 1);
+                        heavy[2 * slot] = g;
+                        heavy[2 * slot + 1] = p;
+                    } else {
+                        light_pick(g, level, p);
+                    }
                 }
+                ++p;
             }
-            ++p;
         }
         __syncthreads();
         const int nh = s_nheavy;
-        for (int h = 0; h < nh; ++h) heavy_pick(heavy[2 * h], level, heavy[2 * h + 1]);
+        for (int h = warp; h < nh; h += NI_T / 32) heavy_pick(heavy[2 * h], level, heavy[2 * h + 1]);
         selected += min(total, pop_size - selected);
-        __syncthreads();
+        if (nh) __syncthreads();                                            // (uniform) the warps' updates of rho before the next minimum
     }
     __syncthreads();
     // survivors: rank < last_rank, ascending index, first pop_size (:202-204)
@@ -377,7 +404,7 @@ k_niche_loop(int* __restrict__ rank, const float* __restrict__ gdist, const int*
 }
 
 struct NicheLayout {
-    size_t rank, rho, rho_last, off, heavy, keysA, keysB, valsA, valsB, taken, tmp, tmp_bytes, total;
+    size_t rank, rho, rho_last, off, heavy, live, keysA, keysB, valsA, valsB, taken, tmp, tmp_bytes, total;
 };
 static NicheLayout niche_layout(int64_t n, int64_t R) {
     NicheLayout L{};
@@ -388,11 +415,12 @@ static NicheLayout niche_layout(int64_t n, int64_t R) {
     L.rho_last = take(sizeof(int) * (size_t)(R + 1));
     L.off = take(sizeof(int) * (size_t)(R + 1));
     L.heavy = take(sizeof(int) * 2 * (size_t)(R + 1));
+    L.live = take(sizeof(int) * (size_t)(R + 1));
     L.keysA = take(sizeof(uint32_t) * (size_t)n);
     L.keysB = take(sizeof(uint32_t) * (size_t)n);
     L.valsA = take(sizeof(int) * (size_t)n);
     L.valsB = take(sizeof(int) * (size_t)n);
-    L.taken = take((size_t)n);
+    L.taken = take(sizeof(uint32_t) * ((size_t)n / 32 + 2));
     cub::DeviceRadixSort::SortPairs(nullptr, L.tmp_bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, (const int*)nullptr,
                                     (int*)nullptr, (int)n);
     L.tmp = take(L.tmp_bytes);
@@ -450,11 +478,12 @@ extern "C" int evx_nsga3_niche(const int32_t* rank, int32_t last_rank, const int
     uint32_t* kB = reinterpret_cast<uint32_t*>(base + L.keysB);
     int* vA = reinterpret_cast<int*>(base + L.valsA);
     int* vB = reinterpret_cast<int*>(base + L.valsB);
-    uint8_t* taken = reinterpret_cast<uint8_t*>(base + L.taken);
+    uint32_t* taken = reinterpret_cast<uint32_t*>(base + L.taken);
+    int* live = reinterpret_cast<int*>(base + L.live);
     EVX_CUDA(cudaMemcpyAsync(rk, rank, sizeof(int) * (size_t)n, cudaMemcpyDeviceToDevice, s));
     EVX_CUDA(cudaMemsetAsync(rho, 0, sizeof(int) * (size_t)(nref + 1), s));
     EVX_CUDA(cudaMemsetAsync(rho_last, 0, sizeof(int) * (size_t)(nref + 1), s));
-    EVX_CUDA(cudaMemsetAsync(taken, 0, (size_t)n, s));
+    EVX_CUDA(cudaMemsetAsync(taken, 0, sizeof(uint32_t) * ((size_t)n / 32 + 2), s));
     k_niche_counts<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(rk, group_id, (int)n, (int)nref, last_rank, rho, rho_last, kA, vA);
     EVX_LAUNCH_CHECK();
     int bits = 1;
@@ -462,7 +491,7 @@ extern "C" int evx_nsga3_niche(const int32_t* rank, int32_t last_rank, const int
     size_t tb = L.tmp_bytes;
     EVX_CUDA(cub::DeviceRadixSort::SortPairs(base + L.tmp, tb, kA, kB, vA, vB, (int)n, 0, bits, s));
     k_niche_loop<<<1, NI_T, 0, s>>>(rk, group_dist, vB, (int)n, (int)nref, last_rank, (int)pop_size, rho, rho_last, off, taken,
-                                    rand_words, selected_idx, nullptr, heavy);
+                                    rand_words, selected_idx, nullptr, heavy, live);
     EVX_LAUNCH_CHECK();
     return EVX_OK;
 }
