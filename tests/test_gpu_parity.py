@@ -76,6 +76,29 @@ def test_nds_random_vs_oracle(E, n, m):
     assert bad.size == 0, (n, m, bad[:10], r[bad[:10]], ref[bad[:10]])
 
 
+@pytest.mark.parametrize("n,m,kind", [(8192, 3, "random"), (8193, 3, "random"), (7000, 6, "random"), (7000, 7, "random"),
+                                      (8000, 3, "ties"), (8192, 2, "one_front"), (6000, 3, "nan")])
+def test_nds_small_population_paths_agree(E, n, m, kind, monkeypatch):
+    """Up to 8192 rows the sort takes two single-CTA kernels (k_small_sort_unique for M <= 6, k_peel_single);
+    EVX_PREP=radix / EVX_PEEL=dynamic switch them off.  All combinations and the oracle must agree, at the
+    limits of both kernels."""
+    from oracle import oracle_c as C
+    rng = np.random.default_rng(n + m)
+    x = rng.random((n, m), dtype=np.float32)
+    if kind == "ties":
+        x = rng.integers(0, 15, (n, m)).astype(np.float32)
+    elif kind == "one_front":
+        x[:, 1] = 1.0 - x[:, 0]
+    elif kind == "nan":
+        x[::13, 2] = np.nan
+    ref = C.non_dominated_sort(x)
+    for prep, peel in (("", ""), ("radix", ""), ("", "dynamic"), ("radix", "dynamic")):
+        monkeypatch.setenv("EVX_PREP", prep)
+        monkeypatch.setenv("EVX_PEEL", peel)
+        r = E.operators.non_dominated_sort(_cuda(x)).cpu().numpy()
+        assert (r == ref).all(), (prep, peel, np.nonzero(r != ref)[0][:10])
+
+
 @pytest.mark.parametrize("kind", ["ties", "dupes", "inf", "nan", "signed_zero", "one_front", "chain", "all_equal"])
 def test_nds_edge_cases(E, kind):
     from oracle import oracle_c as C
