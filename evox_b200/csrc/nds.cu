@@ -215,15 +215,21 @@ __global__ void k_scatter_unique(const float* __restrict__ x, const int* __restr
 }
 
 // ---- small populations: sort + unique in ONE launch ----------------------------------------------------
-// Up to PREP_SMALL_MAX_N rows the M stable radix sorts cost 7 launches each and every onesweep pass
+// Up to 8192 rows, while the keys fit into one CTA's shared memory (M <= 6 at 8192 rows, M <= 13 at 4096, ...), this replaces
+// the radix path: there the M stable radix sorts cost 7 launches each and every onesweep pass
 // ~10 us of latency on a handful of tiles (12 of them at M = 3: 0.13 ms at N = 6000, a quarter of the
 // whole sort).  Here one CTA holds all keys in shared memory and bitonic-sorts the row indices by
 // (key_0, .., key_{M-1}, index) - a total order, so the result is the stable lexicographic order the
 // radix passes give - then marks the heads of runs of equal keys, scans, and scatters the unique rows
 // (k_mark_heads + InclusiveSum + k_scatter_unique).
-constexpr int PREP_SMALL_MAX_N = 8192;
-constexpr int PREP_SMALL_MAX_M = 6;               // keys of 8192 rows x 6 objectives = 192 KB of shared memory
+constexpr int PREP_SMALL_MAX_N = 8192;            // (16 384 rows fit at M = 3, but 105 bitonic stages are no faster than the radix path)
+constexpr size_t PREP_SMALL_MAX_SMEM = 227 * 1024 - 256;   // keys [m][n] + row indices: 8192 rows x 6 objectives, 4096 x 13, ...
 constexpr int SU_T = 1024, SU_ITEMS = PREP_SMALL_MAX_N / SU_T;
+static size_t small_prep_smem(int64_t n, int m) {
+    int64_t pw2 = 1;
+    while (pw2 < n) pw2 <<= 1;
+    return sizeof(uint32_t) * (size_t)m * (size_t)n + sizeof(uint16_t) * (size_t)pw2;
+}
 
 __global__ void __launch_bounds__(SU_T, 1)
 k_small_sort_unique(const float* __restrict__ x, const uint32_t* __restrict__ keys, int n, int m, int64_t npad, Scal* scal,
@@ -2290,10 +2296,8 @@ static int build(const Plan& P, const float* x, cudaStream_t s, cudaEvent_t tile
     int* idx_nxt = P.at<int>(L.idxB);
     k_make_keys<<<gn, T, 0, s>>>(x, n, m, keys, idx_cur, scal);
     EVX_LAUNCH_CHECK();
-    if (n <= PREP_SMALL_MAX_N && m <= PREP_SMALL_MAX_M && !force_radix_prep()) {
-        int pw2 = 1;
-        while (pw2 < n) pw2 <<= 1;
-        const size_t sm = sizeof(uint32_t) * (size_t)m * n + sizeof(uint16_t) * (size_t)pw2;
+    if (n <= PREP_SMALL_MAX_N && small_prep_smem(n, m) <= PREP_SMALL_MAX_SMEM && !force_radix_prep()) {
+        const size_t sm = small_prep_smem(n, m);
         EVX_CUDA(cudaFuncSetAttribute(k_small_sort_unique, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
         k_small_sort_unique<<<1, SU_T, sm, s>>>(x, keys, (int)n, m, L.npad, scal, P.at<float>(L.tcols), P.at<int>(L.row2u));
         EVX_LAUNCH_CHECK();

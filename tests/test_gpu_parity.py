@@ -79,7 +79,7 @@ def test_nds_random_vs_oracle(E, n, m):
 @pytest.mark.parametrize("n,m,kind", [(8192, 3, "random"), (8193, 3, "random"), (7000, 6, "random"), (7000, 7, "random"),
                                       (8000, 3, "ties"), (8192, 2, "one_front"), (6000, 3, "nan")])
 def test_nds_small_population_paths_agree(E, n, m, kind, monkeypatch):
-    """Up to 8192 rows the sort takes two single-CTA kernels (k_small_sort_unique for M <= 6, k_peel_single);
+    """Up to 8192 rows the sort takes two single-CTA kernels (k_small_sort_unique while the keys fit in shared memory - M <= 6 at 8192 rows -, k_peel_single);
     EVX_PREP=radix / EVX_PEEL=dynamic switch them off.  All combinations and the oracle must agree, at the
     limits of both kernels."""
     from oracle import oracle_c as C
