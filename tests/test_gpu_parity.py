@@ -99,7 +99,8 @@ def test_nds_small_population_paths_agree(E, n, m, kind, monkeypatch):
         assert (r == ref).all(), (prep, peel, np.nonzero(r != ref)[0][:10])
 
 
-@pytest.mark.parametrize("kind", ["ties", "dupes", "inf", "nan", "signed_zero", "one_front", "chain", "all_equal"])
+@pytest.mark.parametrize("kind", ["ties", "dupes", "inf", "nan", "signed_zero", "one_front", "chain", "all_equal", "all_nan",
+                                  "one_valid"])
 def test_nds_edge_cases(E, kind):
     from oracle import oracle_c as C
     rng = np.random.default_rng(99)
@@ -126,6 +127,11 @@ def test_nds_edge_cases(E, kind):
         x = (np.arange(n, dtype=np.float32)[:, None] * np.ones((1, 3), np.float32))[rng.permutation(n)]
     elif kind == "all_equal":
         x[:] = 0.25
+    elif kind == "all_nan":
+        x[:, 1] = np.nan
+    elif kind == "one_valid":
+        x[:, 2] = np.nan
+        x[1234] = 0.5
     r = E.operators.non_dominated_sort(_cuda(x)).cpu().numpy()
     ref = C.non_dominated_sort(x)
     assert (r == ref).all(), (kind, np.nonzero(r != ref)[0][:10])
