@@ -104,3 +104,24 @@ def test_environmental_selection_end_to_end(i):
     got = {tuple(r) for r in f.cpu().numpy().tolist()}
     want = {tuple(r) for r in ofit.tolist()}
     assert len(got & want) >= len(want) - max(2, ps // 10)
+
+
+def test_niche_repeatable():
+    """Same reason as test_nds_small_population_repeatable: the niching loop is one CTA with hand-placed barriers
+    and warps that serve heavy niches side by side."""
+    from evox_b200.algorithms import nsga3
+    rng = np.random.default_rng(11)
+    n, nref, ps = 6000, 40, 3000
+    rank = np.sort(rng.integers(0, 6, n)).astype(np.int32)[rng.permutation(n)]
+    last_rank = int(rank[np.argsort(rank, kind="stable")[ps]])
+    gid = np.minimum(rng.geometric(0.15, n) - 1, nref - 1).astype(np.int32)      # a few crowded niches, many thin ones
+    gid[rank > last_rank] = nref
+    gd = (rng.integers(0, 50, n) / 50).astype(np.float32)
+    gd[rank > last_rank] = np.nan
+    rbits = rng.integers(0, 2**32, (ps + 1, 2), dtype=np.uint64).astype(np.uint32)
+    from oracle import oracle_c  # noqa: F401  (build check only)
+    from oracle import oracle_np as O
+    want = O.nsga3_niche(rank, last_rank, gid, gd, nref, ps, [(int(a), int(b)) for a, b in rbits])
+    args = (_cuda(rank), last_rank, _cuda(gid), _cuda(gd), nref, ps, _cuda(rbits.view(np.int32)))
+    for _ in range(25):
+        assert (nsga3.niche(*args).cpu().numpy() == want).all()
