@@ -13,8 +13,10 @@
 //   4. For labelled rows i, j: block(i) < block(j)  =>  i dominates j  <=>  f_k[i] <= f_k[j] for all
 //      k >= 1 (f0 by the order, strictness by uniqueness); block(i) > block(j) => never; same block:
 //      all M objectives.  Only the block-upper triangle exists.
-//   5. Tiles: a slab of rows (32, or 64 for M > 3) against a 32-column word is classified by its f1
-//      ranges (skip / f1 passes / mixed); f2 is a binary-searched suffix mask; what remains is
+//   5. Tiles, M = 3: per-panel tables (k_panel_tables) turn a row's f2 and f1 tests against a whole
+//      32-column word into one table byte + shift and one selector + byte permute (tile_offdiag_m3,
+//      lane <-> word).  Other M: a slab of rows (32, or 64 for M > 3) against a word is classified by
+//      its f1 ranges (skip / f1 passes / mixed); f2 is a binary-searched suffix mask; what remains is
 //      compared on the FMA pipe (sign of b - a).
 //   6. The bit matrix is stored by column PANELS of TW columns, two panels side by side: pair P holds
 //      rows 0 .. (2P+2)*TW-1 as 256-byte super-rows [panel 2P | panel 2P+1] (a random gather of
@@ -26,12 +28,15 @@
 //      all fronts and re-balances the work over the CTAs for every front; on several GPUs the same
 //      kernel also exchanges front membership over NVLink peer memory.  Fronts are separated by data
 //      dependence on epoch-tagged words, not by a barrier.
+//   8. Up to 8192 rows on one GPU two single-CTA kernels replace the launch- and latency-bound parts:
+//      k_small_sort_unique (step 2 in one launch) and k_peel_single (step 7 without flags between CTAs).
 //
-// File map: geometry and workspace layout - sort / unique / labels - tile kernels (word_fail, f2_mask,
-// slab_out, counts_flush, tile_offdiag, tile_diag) - one-front-per-launch peel (k_front_detect /
-// k_mask_to_list / k_front_apply) -
+// File map: geometry and workspace layout - sort / unique (k_small_sort_unique) / labels / panel tables -
+// tile kernels (word_fail, f2_mask, slab_out, counts_flush, tile_offdiag, tile_offdiag_m3, tile_diag) -
+// one-front-per-launch peel (k_front_detect / k_mask_to_list / k_front_apply) -
 // tagged front words and the persistent load-balanced peel (front_row, peel_commit_seg, publish_pending,
-// k_peel_dynamic) - host side (launch_tiles, build, detect / apply, peel_persistent) - C entry points.
+// merge_tree, k_peel_dynamic) - k_peel_single - host side (launch_tiles, build, detect / apply,
+// peel_persistent) - C entry points.
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
