@@ -353,7 +353,24 @@ k_spea2_truncate(const float* __restrict__ obj, const uint8_t* __restrict__ mask
             }
             __syncthreads();
         }
-        if (owner) rescan_own();
+        // the owner's minimum is stale: its whole warp looks through the owner's rows (n / 1024 of them), lane j
+        // taking every 32nd, instead of the owner walking them alone
+        if (warp == (idx % TR_T) / 32) {
+            const int ot = idx % TR_T;
+            float bv2 = INFINITY;
+            int bi2 = 0x7FFFFFFF;
+            for (int i = ot + TR_T * lane; i < n; i += TR_T * 32) {
+                const float v = nn[i];
+                if (v < bv2 || (v == bv2 && i < bi2)) { bv2 = v; bi2 = i; }
+            }
+#pragma unroll
+            for (int o = 16; o >= 1; o >>= 1) {
+                const float ov = __shfl_xor_sync(0xFFFFFFFFu, bv2, o);
+                const int oi = __shfl_xor_sync(0xFFFFFFFFu, bi2, o);
+                if (ov < bv2 || (ov == bv2 && oi < bi2)) { bv2 = ov; bi2 = oi; }
+            }
+            if (owner) { mv = bv2; mi = bi2; }
+        }
         if (act == TR_REMOVE) ++removed;
         // (the next turn's first barrier orders this turn's reads of sel / action before their next writes)
     }
