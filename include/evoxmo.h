@@ -147,7 +147,8 @@ int evx_spea2_truncation_f32(const float* obj, int64_t n, int32_t m, int64_t k, 
 int evx_nsga3_associate_f32(const float* normalized, const float* ref, int64_t n, int64_t nref, int32_t m,
                             int32_t* group_id, float* group_dist, void* stream);
 /* replaces nsga3.py:148-205: niche counts of the fronts before `last_rank`, then the niche-preserving
- * fill from the last front, one survivor per step (the reference's while_loop), and the final index list.
+ * fill from the last front - the reference's one-survivor-per-iteration while_loop, served here one level
+ * of niche counts per step with the same picks and the same use of the random words - and the final index list.
  * rank: device int32 [n] (not modified); rand_words: device uint32 [2 * (pop_size + 1)], words (2i, 2i+1)
  * = the two 32-bit draws jax.random.randint(keys[i], (), 0, span) consumes, keys = split(state.key,
  * pop_size + 1) (:165) - the caller supplies them so that the PRNG stream stays the host framework's;
