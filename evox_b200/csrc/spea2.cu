@@ -249,7 +249,7 @@ k_spea2_truncate(const float* __restrict__ obj, const uint8_t* __restrict__ mask
                  float* knn_d, int* knn_j, int* cnt, int* ptr, uint8_t* alive, uint8_t* __restrict__ keep) {
     __shared__ float rv[TR_T / 32];
     __shared__ int ri[TR_T / 32];
-    __shared__ int sel, action;
+    __shared__ int sel, action, partner;
     const int M = SpDim<MT>::get(m);
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     for (int i = t; i < n; i += TR_T) alive[i] = mask[i] != 0;
@@ -306,11 +306,34 @@ k_spea2_truncate(const float* __restrict__ obj, const uint8_t* __restrict__ mask
                     act = TR_SEARCH;
                 }
             }
-            if (act == TR_REMOVE) { alive[idx] = 0; nn[idx] = INFINITY; }
+            int pj = -1;
+            if (act == TR_REMOVE) {
+                // the removed row's nearest neighbour, when the two are each other's nearest (the closest pair:
+                // the usual case), shows a dead row from now on and would be the very next arg-min: it is
+                // moved on in this same turn instead of spending a turn of its own on it
+                if (alive[idx] && nn[idx] < INFINITY) {
+                    const int j = nni[idx];
+                    if (alive[j] && nni[j] == idx) pj = j;
+                }
+                alive[idx] = 0;
+                nn[idx] = INFINITY;
+            }
             action = act;
+            partner = pj;
         }
         __syncthreads();
         const int act = action;
+        const int pj = partner;
+        if (pj >= 0 && (pj % TR_T) == t) {            // (its owner; a used-up list is left to the lazy repair)
+            const int c = cnt[pj];
+            int p = ptr[pj] + 1;
+            while (p < c && !alive[knn_j[(size_t)pj * SP_KNN + p]]) ++p;
+            if (p < c) {
+                ptr[pj] = p;
+                nn[pj] = knn_d[(size_t)pj * SP_KNN + p];
+                nni[pj] = knn_j[(size_t)pj * SP_KNN + p];
+            }
+        }
         if (act == TR_SEARCH) {                       // list used up: nearest living row, by the whole CTA
             float xi[SpDim<MT>::CAP];
 #pragma unroll
@@ -355,8 +378,11 @@ k_spea2_truncate(const float* __restrict__ obj, const uint8_t* __restrict__ mask
         }
         // the owner's minimum is stale: its whole warp looks through the owner's rows (n / 1024 of them), lane j
         // taking every 32nd, instead of the owner walking them alone
-        if (warp == (idx % TR_T) / 32) {
-            const int ot = idx % TR_T;
+        for (int which = 0; which < 2; ++which) {
+            const int x = which == 0 ? idx : pj;
+            if (x < 0 || warp != (x % TR_T) / 32) continue;                // (warp-uniform)
+            __syncwarp();                                                   // the partner's owner is a lane of this warp
+            const int ot = x % TR_T;
             float bv2 = INFINITY;
             int bi2 = 0x7FFFFFFF;
             for (int i = ot + TR_T * lane; i < n; i += TR_T * 32) {
@@ -369,7 +395,7 @@ k_spea2_truncate(const float* __restrict__ obj, const uint8_t* __restrict__ mask
                 const int oi = __shfl_xor_sync(0xFFFFFFFFu, bi2, o);
                 if (ov < bv2 || (ov == bv2 && oi < bi2)) { bv2 = ov; bi2 = oi; }
             }
-            if (owner) { mv = bv2; mi = bi2; }
+            if (t == ot) { mv = bv2; mi = bi2; }
         }
         if (act == TR_REMOVE) ++removed;
         // (the next turn's first barrier orders this turn's reads of sel / action before their next writes)

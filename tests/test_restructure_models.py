@@ -107,9 +107,20 @@ def truncation_lazy(obj, k, mask, knn=8):
             nn[idx] = dis[idx, lists[idx][ptr[idx]]] if lists[idx] else np.inf
             nni[idx] = lists[idx][ptr[idx]] if lists[idx] else -1
             continue
+        partner = nni[idx] if (alive[idx] and np.isfinite(nn[idx])) else -1
         alive[idx] = False
         nn[idx] = np.inf
         removed += 1
+        # the removed row's nearest neighbour, if the two were each other's nearest, is moved on in the same turn
+        # (a used-up list is left to the lazy repair above)
+        if partner >= 0 and alive[partner] and nni[partner] == idx:
+            p = ptr[partner] + 1
+            while p < len(lists[partner]) and not alive[lists[partner][p]]:
+                p += 1
+            if p < len(lists[partner]):
+                ptr[partner] = p
+                nn[partner] = dis[partner, lists[partner][p]]
+                nni[partner] = lists[partner][p]
     return alive
 
 
