@@ -121,3 +121,83 @@ def test_partition_edge_cases():
     simulate([32 * 5000], 296)                                   # one huge pair shared by every CTA
     simulate([1] * 500, 296)                                     # only single-group pairs
     simulate([32 * WPG, 32 * WPG + 1] * 50, 148)                 # both sides of the warp-pair threshold
+
+
+# ---- k_peel_single and k_small_sort_unique: the index arithmetic of the two single-CTA kernels -------------
+def _cconst(name):
+    m = re.search(rf"constexpr int {name} = (\d+)", SRC)
+    assert m, name
+    return int(m.group(1))
+
+
+@pytest.mark.parametrize("nq", [1, 2, 3, 4])
+@pytest.mark.parametrize("rows", [0, 1, 7, 8, 9, 127, 128, 1016, 1017, 2033, 4065, 8192])
+def test_single_cta_peel_covers_every_list_position_once(nq, rows):
+    """k_peel_single: warps of a pair = row shares x 8 column shares, lanes = 8 row slots x 4 pieces; a lane of
+    row share rs and slot s takes list positions base + rs*8 + s + stride*u (u < 127 per pass).  Every position
+    below `rows` must be taken by exactly one (row share, slot, pass, u) - for each of the 8 x 4 column pieces."""
+    lane_rows = _cconst("PS_LANE_ROWS")
+    W = 32 if nq <= 1 else 16 if nq == 2 else 8
+    RS = W // 8
+    stride = 8 * RS
+    nf = max(rows, 1)
+    passes = (nf + stride * lane_rows - 1) // (stride * lane_rows)
+    seen = np.zeros(rows, int)
+    for p in range(passes):
+        base = p * stride * lane_rows
+        if rows <= base:
+            continue
+        most = min(lane_rows, (rows - base + stride - 1) // stride)
+        for rs in range(RS):
+            for slot in range(8):
+                first = base + rs * 8 + slot
+                for u in range(most):
+                    pos = first + u * stride
+                    if pos < rows:
+                        seen[pos] += 1
+    assert (seen == 1).all()
+    # words of the super-row: column share cs (8 words) x piece q (2 words) tile the 64 words
+    words = sorted(cs * 8 + 2 * q + h for cs in range(8) for q in range(4) for h in range(2))
+    assert words == list(range(64))
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 100, 1025, 4096, 5000, 8192])
+def test_single_cta_bitonic_network_sorts(n):
+    """k_small_sort_unique: the compare-exchange schedule (q-th index with bit j clear, direction by bit k) and
+    the sentinel rule (index >= n sorts after every row), replayed on random keys with duplicates."""
+    rng = np.random.default_rng(n)
+    keys = rng.integers(0, max(2, n // 3), n)                       # many equal keys: the index decides
+    P = 1
+    while P < n:
+        P <<= 1
+    idx = np.arange(P)
+
+    def before(a, b):
+        if a >= n or b >= n:
+            return a < b
+        if keys[a] != keys[b]:
+            return keys[a] < keys[b]
+        return a < b
+
+    k = 2
+    while k <= P:
+        j = k >> 1
+        while j > 0:
+            q = np.arange(P >> 1)
+            i = ((q & ~(j - 1)) << 1) | (q & (j - 1))
+            assert ((i & j) == 0).all() and len(np.unique(i)) == len(i)
+            a, b = idx[i].copy(), idx[i | j].copy()
+            up = (i & k) == 0
+            if n <= 1100:                                             # scalar compare for the small cases
+                swap = np.array([before(int(bb), int(aa)) == bool(uu) for aa, bb, uu in zip(a, b, up)])
+            else:
+                ka = np.where(a < n, keys[np.minimum(a, n - 1)], np.iinfo(np.int64).max)
+                kb = np.where(b < n, keys[np.minimum(b, n - 1)], np.iinfo(np.int64).max)
+                b_before_a = (kb < ka) | ((kb == ka) & (b < a))
+                swap = b_before_a == up
+            idx[i] = np.where(swap, b, a)
+            idx[i | j] = np.where(swap, a, b)
+            j >>= 1
+        k <<= 1
+    want = np.concatenate([np.argsort(keys, kind="stable"), np.arange(n, P)])
+    assert (idx == want).all()
