@@ -5,9 +5,10 @@
 // the one-survivor-per-iteration `while_loop`, up to pop_size sequential steps, each of which touches
 // several arrays of N elements in the reference).  The normalisation before it (:103-139: ideal point,
 // extreme points, a tiny M x M solve) stays host glue.
-//   associate - a thread takes up to four solutions, reference directions are staged in shared memory already
-//               divided by their norm; nothing N x R is stored.  The distance is monotone in 1 - c^2, so the
-//               square root is only taken when a direction improves on the best so far.
+//   associate - a thread takes up to four solutions, the reference directions are staged in shared memory
+//               already divided by their norm and split eight ways over the CTA's warps; nothing N x R is
+//               stored.  The distance is monotone in 1 - c^2, so the square root is only taken when a
+//               direction improves on the best so far.
 //   niche     - the last front's members are sorted by (group, index) once (radix sort); one persistent
 //               CTA then runs the reference's loop LEVEL BY LEVEL instead of pick by pick: the loop always
 //               serves the first niche with the smallest count, so all niches at the smallest count c are
@@ -66,36 +67,44 @@ k_nsga3_associate(const float* __restrict__ x, const float* __restrict__ ref, in
     if (i < n) { gid[i] = bi; gdist[i] = best; }
 }
 
-// The same for a compile-time number of objectives: RPT solutions per thread (each staged direction is read
-// once for all of them), FMA dot product, and d = |x| sqrt(1 - c^2) only when 1 - c^2 is below the best
-// direction's (sqrt and the product are monotone under round-to-nearest, so a direction with a larger or
-// equal 1 - c^2 can never be strictly closer: the first minimum is unchanged).
+// The same for a compile-time number of objectives.  A CTA takes 32 * RPT solutions (lane r: solutions
+// q * 32 + r) and splits the reference directions eight ways over its warps (warp sp: 16 of every 128 staged
+// directions), so that 100 000 solutions still fill the chip and each staged direction is read once for RPT
+// solutions; FMA dot product; d = |x| sqrt(1 - c^2) only when 1 - c^2 is below the split's best so far (sqrt
+// and the product are monotone under round-to-nearest, so a direction with a larger or equal 1 - c^2 can
+// never be strictly closer: the first minimum is unchanged).  The eight splits' results are merged by
+// (distance, direction index): the first minimum over all directions.
+constexpr int AS_SPLIT = AS_T / 32;
 template <int M, int RPT>
 __global__ void __launch_bounds__(AS_T)
 k_nsga3_associate_t(const float* __restrict__ x, const float* __restrict__ ref, int n, int R, int* __restrict__ gid,
                     float* __restrict__ gdist) {
     extern __shared__ float tile[];                   // [AS_TILE][M]
+    __shared__ float md[AS_SPLIT][32 * RPT];
+    __shared__ int mi[AS_SPLIT][32 * RPT];
+    const int r = threadIdx.x & 31, sp = threadIdx.x >> 5;
     float xn[RPT][M], nx[RPT], best[RPT], best_s[RPT];
     int bi[RPT];
 #pragma unroll
-    for (int r = 0; r < RPT; ++r) {
-        const int i = (blockIdx.x * RPT + r) * AS_T + threadIdx.x;
-        nx[r] = 0.0f;
-        best[r] = __int_as_float(0x7FC00000);         // NaN until a number is seen
-        best_s[r] = INFINITY;
-        bi[r] = R;
+    for (int q = 0; q < RPT; ++q) {
+        const int i = blockIdx.x * (32 * RPT) + q * 32 + r;
+        nx[q] = 0.0f;
+        best[q] = __int_as_float(0x7FC00000);         // NaN until a number is seen
+        best_s[q] = INFINITY;
+        bi[q] = R;
         if (i < n) {
             float acc = 0.0f;
 #pragma unroll
-            for (int k = 0; k < M; ++k) { xn[r][k] = x[(size_t)i * M + k]; acc = __fadd_rn(acc, __fmul_rn(xn[r][k], xn[r][k])); }
-            nx[r] = __fsqrt_rn(acc);
+            for (int k = 0; k < M; ++k) { xn[q][k] = x[(size_t)i * M + k]; acc = __fadd_rn(acc, __fmul_rn(xn[q][k], xn[q][k])); }
+            nx[q] = __fsqrt_rn(acc);
 #pragma unroll
-            for (int k = 0; k < M; ++k) xn[r][k] = __fdiv_rn(xn[r][k], nx[r]);
+            for (int k = 0; k < M; ++k) xn[q][k] = __fdiv_rn(xn[q][k], nx[q]);
         } else {
 #pragma unroll
-            for (int k = 0; k < M; ++k) xn[r][k] = __int_as_float(0x7FC00000);      // never improves
+            for (int k = 0; k < M; ++k) xn[q][k] = __int_as_float(0x7FC00000);      // never improves
         }
     }
+    constexpr int PER = AS_TILE / AS_SPLIT;           // directions of a tile per split
     for (int r0 = 0; r0 < R; r0 += AS_TILE) {
         const int nt = min(AS_TILE, R - r0);
         __syncthreads();
@@ -109,38 +118,48 @@ k_nsga3_associate_t(const float* __restrict__ x, const float* __restrict__ ref, 
             for (int k = 0; k < M; ++k) tile[t * M + k] = __fdiv_rn(y[k], ny);
         }
         __syncthreads();
-        for (int t = 0; t < nt; ++t) {
+        const int te = min(nt, (sp + 1) * PER);
+        for (int t = sp * PER; t < te; ++t) {
             float y[M];
 #pragma unroll
             for (int k = 0; k < M; ++k) y[k] = tile[t * M + k];
 #pragma unroll
-            for (int r = 0; r < RPT; ++r) {
-                float c = __fmul_rn(xn[r][0], y[0]);
+            for (int q = 0; q < RPT; ++q) {
+                float c = __fmul_rn(xn[q][0], y[0]);
 #pragma unroll
-                for (int k = 1; k < M; ++k) c = __fmaf_rn(xn[r][k], y[k], c);
+                for (int k = 1; k < M; ++k) c = __fmaf_rn(xn[q][k], y[k], c);
                 const float sq = __fmaf_rn(-c, c, 1.0f);
-                if (sq < best_s[r]) {                                           // false for NaN
-                    const float d = __fmul_rn(nx[r], __fsqrt_rn(sq));
-                    if (d == d && !(best[r] <= d)) { best[r] = d; best_s[r] = sq; bi[r] = r0 + t; }
+                if (sq < best_s[q]) {                                           // false for NaN
+                    const float d = __fmul_rn(nx[q], __fsqrt_rn(sq));
+                    if (d == d && !(best[q] <= d)) { best[q] = d; best_s[q] = sq; bi[q] = r0 + t; }
                 }
             }
         }
     }
 #pragma unroll
-    for (int r = 0; r < RPT; ++r) {
-        const int i = (blockIdx.x * RPT + r) * AS_T + threadIdx.x;
-        if (i < n) { gid[i] = bi[r]; gdist[i] = best[r]; }
+    for (int q = 0; q < RPT; ++q) { md[sp][q * 32 + r] = best[q]; mi[sp][q * 32 + r] = bi[q]; }
+    __syncthreads();
+    if (sp == 0) {
+#pragma unroll
+        for (int q = 0; q < RPT; ++q) {
+            const int i = blockIdx.x * (32 * RPT) + q * 32 + r;
+            float bd = __int_as_float(0x7FC00000);
+            int bj = R;
+#pragma unroll
+            for (int w = 0; w < AS_SPLIT; ++w) {
+                const float d = md[w][q * 32 + r];
+                const int j = mi[w][q * 32 + r];
+                if (j < R && (bj == R || d < bd || (d == bd && j < bj))) { bd = d; bj = j; }
+            }
+            if (i < n) { gid[i] = bj; gdist[i] = bd; }
+        }
     }
 }
 
 template <int M>
 static void launch_associate_t(const float* x, const float* ref, int n, int R, int* gid, float* gd, cudaStream_t s) {
     constexpr int RPT = M <= 12 ? 4 : 2;
-    // small populations: fewer rows per thread so that the grid still covers the chip
-    if ((int64_t)n >= (int64_t)148 * 4 * AS_T * RPT)
-        k_nsga3_associate_t<M, RPT><<<(unsigned)ceil_div(n, AS_T * RPT), AS_T, sizeof(float) * AS_TILE * M, s>>>(x, ref, n, R, gid, gd);
-    else
-        k_nsga3_associate_t<M, 1><<<(unsigned)ceil_div(n, AS_T), AS_T, sizeof(float) * AS_TILE * M, s>>>(x, ref, n, R, gid, gd);
+    k_nsga3_associate_t<M, RPT><<<(unsigned)ceil_div(n, 32 * RPT), AS_T, sizeof(float) * AS_TILE * M, s>>>(x, ref, n, R, gid, gd);
 }
 
 // ---- niching ------------------------------------------------------------------------------------------
